@@ -1,0 +1,147 @@
+/*
+ * svmb200.h -- C ABI of the B200-native RBF-kernel SMO trainer (libsvmb200.so).
+ *
+ * This is the drop-in boundary for the reference's solver path.  The reference has
+ * no FFI; the interface it does have is the free function
+ *
+ *     void SMO_train(const vector<double>& x_train, const vector<int>& y_train, size_t n_features,
+ *                    vector<double>& alpha, double& b, double C = 10.0 [, bool init = true]);
+ *                                            (code/main3.cpp:162, code/mpi_svm_main2.cpp:154)
+ *
+ * plus find_min_max / scale_features (code/main3.cpp:57,74), get_SV_indices (:297) and the
+ * prediction loop of main() (:391-405).  Each entry point below names the reference lines it
+ * replaces.  All pointers are HOST pointers unless the name says "dev"; every buffer is owned by
+ * the caller.  Every function returns 0 on success and a negative SVMB200_E* code on failure (the
+ * message is available from svmb200_last_error).  As in the reference, abnormal solver stops are
+ * not errors: they are reported in svmb200_stats.stop_reason (code/main3.cpp:205-209,246-257,
+ * 283-287 print to cerr, break, and still return b).
+ *
+ * Not thread-safe per context; independent contexts may be used from different threads.
+ * There is no CPU fallback: without a CUDA device every call fails with SVMB200_ENODEVICE.
+ */
+#ifndef SVMB200_H
+#define SVMB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVMB200_OK          0
+#define SVMB200_EINVAL     -1   /* bad argument                                   */
+#define SVMB200_ECUDA      -2   /* a CUDA runtime call failed                     */
+#define SVMB200_ENODEVICE  -3   /* no usable CUDA device                          */
+#define SVMB200_ESTATE     -4   /* call order violated (e.g. train before upload) */
+#define SVMB200_ELIMIT     -5   /* size beyond a documented limit                 */
+
+/* stop_reason values: the five ways code/main3.cpp's loop ends */
+#define SVMB200_STOP_CONVERGED   0  /* b_low <= b_high + 2 tau              main3.cpp:213 */
+#define SVMB200_STOP_NOT_FOUND   1  /* i_high or i_low not found            main3.cpp:205 */
+#define SVMB200_STOP_INFEASIBLE  2  /* infeasible U and V                   main3.cpp:246 */
+#define SVMB200_STOP_ETA         3  /* non positive eta                     main3.cpp:253 */
+#define SVMB200_STOP_MAX_ITER    4  /* num_iter > max_iter                  main3.cpp:283 */
+
+typedef struct svmb200_ctx svmb200_ctx;
+
+/* The reference's literals as parameters; svmb200_default_params fills in those literals:
+ * C=10 (main3.cpp:163,342) gamma=0.00125 (:95) eps=1e-12 (:109,128,165) tau=1e-5 (:196)
+ * max_iter=100000 (:198) sv_tol=1e-8 (:297,367). */
+typedef struct {
+    double  C;
+    double  gamma;
+    double  eps;
+    double  tau;
+    int32_t max_iter;
+    double  sv_tol;
+    int32_t wss;          /* working-set selection: 1 = first-order maximal violating pair, the only
+                             rule the reference has (main3.cpp:107-142).  Other values: EINVAL. */
+    int32_t warm_start;   /* 0: alpha := 0, f := -y (main3.cpp:167-172).  1: alpha is in/out and f is
+                             rebuilt from it (mpi_svm_main2.cpp:167-183, "init = false"). */
+    int32_t cache_rows;   /* HBM kernel-row cache capacity in rows; 0 = off (the reference's behaviour:
+                             only the previous row is reused, main3.cpp:216-232); -1 = auto. */
+    int32_t accum_chunk;  /* fp32 squares summed before widening to FP64: 1, 2 or 4 (DESIGN.md
+                             "Numerics"); 0 = library default. */
+    int32_t trace_cap;    /* record the first trace_cap (i_high, i_low) pairs for svmb200_get_trace */
+    int32_t l2_persist;   /* 0 = stream X with evict-first; 1 = keep a leading fraction of every
+                             block's rows resident in L2 (evict-last); -1 = auto */
+} svmb200_params;
+
+typedef struct {
+    int32_t num_iter;        /* the reference's printed counter: starts at 1, +1 per update (main3.cpp:197,281) */
+    int32_t stop_reason;     /* SVMB200_STOP_* */
+    int64_t i_high, i_low;   /* last selected pair (n if not found) */
+    double  b_high, b_low;
+    double  smo_ms;          /* device time of the SMO loop alone (CUDA events) */
+    double  init_ms;         /* device time of state init (+ warm-start f rebuild) */
+    int64_t x_passes;        /* iterations that streamed X (both kernel rows recomputed) */
+    int64_t cache_hits;      /* iterations served entirely from the row cache */
+    int64_t x_bytes_streamed;/* x_passes * n * row_pitch_bytes */
+    int32_t n_sv;            /* count of alpha > sv_tol */
+    int32_t grid_blocks;     /* persistent grid actually launched */
+    int32_t launches;        /* kernels launched by this call */
+} svmb200_stats;
+
+void svmb200_default_params(svmb200_params *p);
+
+/* Context bound to one CUDA device ordinal. */
+int  svmb200_create(svmb200_ctx **out, int device);
+void svmb200_destroy(svmb200_ctx *ctx);
+const char *svmb200_last_error(const svmb200_ctx *ctx);   /* ctx may be NULL: last create error */
+const char *svmb200_version(void);
+
+/* ---- ingest + preprocessing: replaces find_min_max + scale_features (main3.cpp:57-89,338-339)
+ * and the reference GPU's four scratch copies of X (gpu_svm_main3.cu:538-598).  X is row-major
+ * [n x d]; y is +-1 (main3.cpp:49-52 maps "label != 1 -> -1" before the solver sees it).  The
+ * device computes per-feature min/max in FP64, scales (x-min)/range with range<1e-12 -> 1 in FP64
+ * and stores fp32 rows padded to a multiple of 4 floats.  min_out/max_out (optional, d doubles)
+ * receive the statistics; they are also kept in the context for svmb200_predict_*. */
+int svmb200_set_train_u8 (svmb200_ctx *ctx, const uint8_t *X, const int32_t *y, int64_t n, int32_t d,
+                          double *min_out, double *max_out);
+int svmb200_set_train_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y, int64_t n, int32_t d,
+                          double *min_out, double *max_out);
+/* X already scaled by the caller -- exactly what the reference's SMO_train receives
+ * (main3.cpp:347).  No statistics are computed; svmb200_predict_scaled_f64 is the matching call. */
+int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y, int64_t n, int32_t d);
+
+/* ---- the solver: replaces SMO_train (main3.cpp:162-294; warm start mpi_svm_main2.cpp:154-288).
+ * alpha: n doubles, written on return; read first when params->warm_start != 0.  b: (b_high+b_low)/2
+ * (main3.cpp:291).  stats may be NULL. */
+int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params, double *alpha, double *b,
+                      svmb200_stats *stats);
+
+/* ---- replaces get_SV_indices (main3.cpp:297-304) on the last trained alpha: ascending row
+ * indices with alpha > sv_tol.  ids may be NULL to query the count. */
+int svmb200_sv_ids(svmb200_ctx *ctx, int32_t *ids, int32_t cap, int32_t *count);
+
+/* ---- decision function + accuracy: replaces main3.cpp:391-405 (ge_zero = 0: "curr > 0") and
+ * mpi_svm_main2.cpp:721-733 (ge_zero = 1: "s >= 0") and the reference GPU's predict/reduce_sum
+ * (gpu_svm_main3.cu:277-315).  Test rows are scaled with the TRAIN statistics (main3.cpp:355).
+ * Uses the support vectors and b of the last svmb200_smo_train.  y_test may be NULL (then *correct
+ * is 0); scores (optional) receives m decision values sum_k alpha_k y_k K(x, x_k) - b. */
+int svmb200_predict_u8 (svmb200_ctx *ctx, const uint8_t *X, const int32_t *y_test, int64_t m,
+                        int32_t ge_zero, int32_t *correct, double *scores);
+int svmb200_predict_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y_test, int64_t m,
+                        int32_t ge_zero, int32_t *correct, double *scores);
+int svmb200_predict_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y_test, int64_t m,
+                               int32_t ge_zero, int32_t *correct, double *scores);
+
+/* ---- introspection used by the parity tests ---- */
+/* (i_high, i_low) of the first min(cap, recorded) iterations that reached the update */
+int svmb200_get_trace(svmb200_ctx *ctx, int32_t *pairs, int32_t cap, int32_t *count);
+/* final error vector f (n doubles) */
+int svmb200_get_f(svmb200_ctx *ctx, double *f);
+/* one kernel row K(i, .) as the solver computes it: the replacement of main3.cpp:221-222 */
+int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_chunk, double *row);
+/* one working-set selection on caller-supplied state: replaces calc_i_high / calc_i_low
+ * (main3.cpp:107-142): lowest index wins ties; n when the set is empty */
+int svmb200_select_pair(svmb200_ctx *ctx, const double *alpha, const double *f, const int32_t *y,
+                        int64_t n, double C, double eps, int64_t *i_high, int64_t *i_low);
+/* the scaled fp32 training matrix as stored in HBM (n x d, padding stripped) */
+int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVMB200_H */

@@ -1,0 +1,360 @@
+/*
+ * oracle/smo_oracle.c -- CPU restatement of the reference's serial SMO (see smo_oracle.h).
+ * TEST INFRASTRUCTURE ONLY: never linked into, loaded by, or called from the product path.
+ *
+ * Build: gcc -O2 -ffp-contract=off -fPIC -shared (oracle/Makefile).  -ffp-contract=off keeps
+ * every FP64 operation separately rounded, as the reference's x86-64 build (g++ -O3, no -mfma,
+ * README.md:139) does.
+ */
+#include "smo_oracle.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+void oracle_default_params(oracle_params *p)
+{
+    p->C = 10.0;          /* code/main3.cpp:163,342 */
+    p->gamma = 0.00125;   /* code/main3.cpp:95      */
+    p->eps = 1e-12;       /* code/main3.cpp:165     */
+    p->tau = 1e-5;        /* code/main3.cpp:196     */
+    p->max_iter = 100000; /* code/main3.cpp:198     */
+    p->sv_tol = 1e-8;     /* code/main3.cpp:367     */
+}
+
+/* code/main3.cpp:92-104 */
+double oracle_kernel(const double *v1, const double *v2, size_t d, double gamma)
+{
+    double res = 0.0;
+    for (size_t i = 0; i < d; ++i)
+        res += (v1[i] - v2[i]) * (v1[i] - v2[i]);
+    return exp(-gamma * res);
+}
+
+/* code/main3.cpp:57-71 */
+void oracle_find_min_max(const double *x, double *min_val, double *max_val, size_t n, size_t d)
+{
+    for (size_t j = 0; j < d; ++j) {
+        double lo = x[j], hi = x[j];
+        for (size_t i = 0; i < n; ++i) {
+            double v = x[i * d + j];
+            lo = v < lo ? v : lo; /* std::min(a,b) = (b<a)?b:a */
+            hi = hi < v ? v : hi; /* std::max(a,b) = (a<b)?b:a */
+        }
+        min_val[j] = lo;
+        max_val[j] = hi;
+    }
+}
+
+/* code/main3.cpp:74-89 */
+void oracle_scale_features(double *x, const double *min_val, const double *max_val, size_t n, size_t d)
+{
+    for (size_t j = 0; j < d; ++j) {
+        double range = max_val[j] - min_val[j];
+        if (range < 1e-12)
+            range = 1.0;
+        for (size_t i = 0; i < n; ++i)
+            x[i * d + j] = (x[i * d + j] - min_val[j]) / range;
+    }
+}
+
+/* code/main3.cpp:107-123 */
+size_t oracle_calc_i_high(const double *alpha, const int *y, const double *f, size_t n, double C, double eps)
+{
+    size_t ans = n;
+    double best = INFINITY;
+    for (size_t i = 0; i < n; ++i) {
+        int in_set = (y[i] == 1 && alpha[i] < C - eps) || (y[i] == -1 && alpha[i] > 0.0 + eps);
+        if (in_set && f[i] < best) {
+            best = f[i];
+            ans = i;
+        }
+    }
+    return ans;
+}
+
+/* code/main3.cpp:126-142 */
+size_t oracle_calc_i_low(const double *alpha, const int *y, const double *f, size_t n, double C, double eps)
+{
+    size_t ans = n;
+    double best = -INFINITY;
+    for (size_t i = 0; i < n; ++i) {
+        int in_set = (y[i] == 1 && alpha[i] > 0.0 + eps) || (y[i] == -1 && alpha[i] < C - eps);
+        if (in_set && f[i] > best) {
+            best = f[i];
+            ans = i;
+        }
+    }
+    return ans;
+}
+
+/* code/main3.cpp:145-159 */
+int oracle_calculate_U_V(int s, double a_high, double a_low, double C, double *U, double *V)
+{
+    if (s == -1) {
+        double u = a_low - a_high, v = C + a_low - a_high;
+        *U = (0.0 < u) ? u : 0.0; /* std::max(0.0, u) */
+        *V = (v < C) ? v : C;     /* std::min(C, v)   */
+    } else {
+        double u = a_low + a_high - C, v = a_low + a_high;
+        *U = (0.0 < u) ? u : 0.0;
+        *V = (v < C) ? v : C;
+    }
+    return *U <= *V + 1e-12;
+}
+
+/* ------------------------------------------------------------------------------------------
+ * The CUDA path's arithmetic, restated op for op (see DESIGN.md "Numerics").
+ * ------------------------------------------------------------------------------------------ */
+
+/* exp(x) from IEEE-exact primitives only: k = rint(x*log2 e); r = x - k ln2 (two-part, fma);
+ * degree-13 Taylor polynomial in Horner form with fma; scaled by 2^k in two exact-power steps. */
+double oracle_device_exp(double x)
+{
+    if (x != x) return x;
+    if (x > 709.782712893384) return INFINITY;
+    if (x < -745.2) return 0.0;
+    const double LOG2E = 1.4426950408889634;
+    const double LN2_HI = 6.93147180369123816490e-01;
+    const double LN2_LO = 1.90821492927058770002e-10;
+    double kf = rint(x * LOG2E);
+    double r = fma(-kf, LN2_HI, x);
+    r = fma(-kf, LN2_LO, r);
+    double p = 1.0 / 6227020800.0;            /* 1/13! */
+    p = fma(p, r, 1.0 / 479001600.0);         /* 1/12! */
+    p = fma(p, r, 1.0 / 39916800.0);          /* 1/11! */
+    p = fma(p, r, 1.0 / 3628800.0);           /* 1/10! */
+    p = fma(p, r, 1.0 / 362880.0);            /* 1/9!  */
+    p = fma(p, r, 1.0 / 40320.0);             /* 1/8!  */
+    p = fma(p, r, 1.0 / 5040.0);              /* 1/7!  */
+    p = fma(p, r, 1.0 / 720.0);               /* 1/6!  */
+    p = fma(p, r, 1.0 / 120.0);               /* 1/5!  */
+    p = fma(p, r, 1.0 / 24.0);                /* 1/4!  */
+    p = fma(p, r, 1.0 / 6.0);                 /* 1/3!  */
+    p = fma(p, r, 0.5);                       /* 1/2!  */
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    int k = (int)kf;
+    int k1 = k / 2, k2 = k - k1;
+    union { uint64_t u; double f; } s1, s2;
+    s1.u = (uint64_t)(k1 + 1023) << 52;
+    s2.u = (uint64_t)(k2 + 1023) << 52;
+    return (p * s1.f) * s2.f;
+}
+
+static int g_device_chunk = 1; /* fp32 squares summed before widening to FP64: 1, 2 or 4 */
+void oracle_set_device_chunk(int ch) { g_device_chunk = (ch == 2 || ch == 4) ? ch : 1; }
+int oracle_get_device_chunk(void) { return g_device_chunk; }
+
+double oracle_device_sqdist(const float *a, const float *b, size_t d)
+{
+    double lane[32];
+    for (int l = 0; l < 32; ++l) lane[l] = 0.0;
+    size_t d4 = (d + 3) / 4;
+    for (size_t q = 0; q < d4; ++q) {
+        float df[4];
+        for (int c = 0; c < 4; ++c) {
+            size_t k = 4 * q + c;
+            float av = k < d ? a[k] : 0.0f, bv = k < d ? b[k] : 0.0f; /* rows are zero-padded */
+            df[c] = av - bv;
+        }
+        double acc = lane[q & 31];
+        if (g_device_chunk == 4) {
+            float p = df[0] * df[0];
+            p = fmaf(df[1], df[1], p);
+            p = fmaf(df[2], df[2], p);
+            p = fmaf(df[3], df[3], p);
+            acc = acc + (double)p;
+        } else if (g_device_chunk == 2) {
+            float p = df[0] * df[0];
+            p = fmaf(df[1], df[1], p);
+            acc = acc + (double)p;
+            float t = df[2] * df[2];
+            t = fmaf(df[3], df[3], t);
+            acc = acc + (double)t;
+        } else {
+            for (int c = 0; c < 4; ++c) {
+                double e = (double)df[c];
+                acc = fma(e, e, acc);
+            }
+        }
+        lane[q & 31] = acc;
+    }
+    for (int off = 16; off >= 1; off >>= 1) {
+        double t[32];
+        for (int l = 0; l < 32; ++l) t[l] = lane[l] + lane[l ^ off];
+        for (int l = 0; l < 32; ++l) lane[l] = t[l];
+    }
+    return lane[0];
+}
+
+double oracle_device_kernel(const float *a, const float *b, size_t d, double gamma)
+{
+    return oracle_device_exp(-gamma * oracle_device_sqdist(a, b, d));
+}
+
+/* one kernel row K(i, .) in the chosen arithmetic */
+static void kernel_row(const double *x, const float *x32, size_t n, size_t d, size_t i,
+                       double gamma, int arith, double *row)
+{
+    if (arith == ORACLE_ARITH_F64) {
+        for (size_t j = 0; j < n; ++j)
+            row[j] = oracle_kernel(x + i * d, x + j * d, d, gamma);
+    } else {
+        for (size_t j = 0; j < n; ++j)
+            row[j] = oracle_device_kernel(x32 + i * d, x32 + j * d, d, gamma);
+    }
+}
+
+/* code/main3.cpp:162-294 ; warm start code/mpi_svm_main2.cpp:161-184 */
+int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
+                     double *alpha, double *b, const oracle_params *p, int init,
+                     int arith, oracle_result *res,
+                     int32_t *trace, size_t trace_cap, double *f_out)
+{
+    const double eps = p->eps, C = p->C, tau = p->tau, gamma = p->gamma;
+    double *f = (double *)malloc(sizeof(double) * (n ? n : 1));
+    double *K_h = (double *)calloc(n ? n : 1, sizeof(double));
+    double *K_l = (double *)calloc(n ? n : 1, sizeof(double));
+    float *x32 = NULL;
+    if (arith == ORACLE_ARITH_DEVICE) {
+        x32 = (float *)malloc(sizeof(float) * (n * d ? n * d : 1));
+        for (size_t k = 0; k < n * d; ++k) x32[k] = (float)x[k];
+    }
+
+    if (init) {
+        for (size_t i = 0; i < n; ++i) {
+            alpha[i] = 0.0;                 /* :167 */
+            f[i] = -(double)y[i];           /* :171-172 */
+        }
+    } else {
+        /* code/mpi_svm_main2.cpp:169-183: f_i = sum_{alpha_j != 0} alpha_j y_j K(x_j, x_i) - y_i */
+        for (size_t i = 0; i < n; ++i) {
+            double sum = 0.0;
+            for (size_t j = 0; j < n; ++j) {
+                if (alpha[j] == 0.0) continue;
+                double kij = (arith == ORACLE_ARITH_F64)
+                                 ? oracle_kernel(x + j * d, x + i * d, d, gamma)
+                                 : oracle_device_kernel(x32 + j * d, x32 + i * d, d, gamma);
+                sum += alpha[j] * y[j] * kij;
+            }
+            f[i] = sum - (double)y[i];
+        }
+    }
+
+    size_t i_high = n, i_low = n;
+    double b_high = 0.0, b_low = 0.0; /* the reference leaves these uninitialised (:188-189) */
+    size_t i_high_prev = n, i_low_prev = n;
+    int num_iter = 1;
+    int stop = ORACLE_STOP_CONVERGED;
+    int64_t rows = 0;
+    size_t ntrace = 0;
+
+    for (;;) {
+        i_high = oracle_calc_i_high(alpha, y, f, n, C, eps); /* :203 */
+        i_low = oracle_calc_i_low(alpha, y, f, n, C, eps);   /* :204 */
+        if (i_high >= n || i_low >= n) { stop = ORACLE_STOP_NOT_FOUND; break; } /* :205 */
+        b_high = f[i_high];
+        b_low = f[i_low];
+        if (b_low <= b_high + 2.0 * tau) { stop = ORACLE_STOP_CONVERGED; break; } /* :213 */
+
+        if (i_high != i_high_prev) { /* :216-223 */
+            i_high_prev = i_high;
+            kernel_row(x, x32, n, d, i_high, gamma, arith, K_h);
+            ++rows;
+        }
+        if (i_low != i_low_prev) { /* :225-232 */
+            i_low_prev = i_low;
+            kernel_row(x, x32, n, d, i_low, gamma, arith, K_l);
+            ++rows;
+        }
+        if (trace && ntrace < trace_cap) {
+            trace[2 * ntrace] = (int32_t)i_high;
+            trace[2 * ntrace + 1] = (int32_t)i_low;
+        }
+        ++ntrace;
+
+        int s = y[i_high] * y[i_low];                    /* :235 */
+        double K11 = K_h[i_high], K22 = K_l[i_low], K12 = K_h[i_low]; /* :239-241 */
+        double eta = K11 + K22 - 2.0 * K12;              /* :243 */
+        double U, V;
+        if (!oracle_calculate_U_V(s, alpha[i_high], alpha[i_low], C, &U, &V)) { /* :246 */
+            stop = ORACLE_STOP_INFEASIBLE; break;
+        }
+        if (eta <= eps) { stop = ORACLE_STOP_ETA; break; } /* :253 */
+
+        double na_low = alpha[i_low] + y[i_low] * (b_high - b_low) / eta; /* :259 */
+        if (na_low > V) na_low = V;
+        if (na_low < U) na_low = U;
+        double na_high = alpha[i_high] + s * (alpha[i_low] - na_low);      /* :266 */
+
+        double d_high = na_high - alpha[i_high];
+        double d_low = na_low - alpha[i_low];
+        for (size_t i = 0; i < n; ++i) /* :271-275 */
+            f[i] += d_high * y[i_high] * K_h[i] + d_low * y[i_low] * K_l[i];
+
+        alpha[i_high] = na_high; /* :278-279 */
+        alpha[i_low] = na_low;
+
+        ++num_iter;              /* :281-287 */
+        if (num_iter > p->max_iter) { stop = ORACLE_STOP_MAX_ITER; break; }
+    }
+
+    *b = (b_high + b_low) / 2; /* :291 */
+    if (res) {
+        res->num_iter = num_iter;
+        res->stop_reason = stop;
+        res->i_high = (int64_t)i_high;
+        res->i_low = (int64_t)i_low;
+        res->b_high = b_high;
+        res->b_low = b_low;
+        res->rows_computed = rows;
+    }
+    if (f_out) memcpy(f_out, f, sizeof(double) * n);
+    free(f); free(K_h); free(K_l); free(x32);
+    return 0;
+}
+
+/* code/main3.cpp:297-304 */
+size_t oracle_sv_indices(const double *alpha, size_t n, double tol, int32_t *idx)
+{
+    size_t c = 0;
+    for (size_t i = 0; i < n; ++i)
+        if (alpha[i] > tol) {
+            if (idx) idx[c] = (int32_t)i;
+            ++c;
+        }
+    return c;
+}
+
+/* code/main3.cpp:391-405 ; code/mpi_svm_main2.cpp:721-733 */
+int oracle_predict(const double *x_test, const int *y_test, size_t m,
+                   const double *x_train, const int *y_train, const double *alpha,
+                   const int32_t *sv_idx, size_t n_sv, size_t d, double gamma, double b,
+                   int ge_zero, int arith, double *scores)
+{
+    int correct = 0;
+    float *t32 = NULL, *s32 = NULL;
+    if (arith == ORACLE_ARITH_DEVICE) {
+        t32 = (float *)malloc(sizeof(float) * (m * d ? m * d : 1));
+        s32 = (float *)malloc(sizeof(float) * (n_sv * d ? n_sv * d : 1));
+        for (size_t k = 0; k < m * d; ++k) t32[k] = (float)x_test[k];
+        for (size_t k = 0; k < n_sv; ++k)
+            for (size_t c = 0; c < d; ++c) s32[k * d + c] = (float)x_train[(size_t)sv_idx[k] * d + c];
+    }
+    for (size_t i = 0; i < m; ++i) {
+        double curr = -b;
+        for (size_t k = 0; k < n_sv; ++k) {
+            size_t j = (size_t)sv_idx[k];
+            double kv = (arith == ORACLE_ARITH_F64)
+                            ? oracle_kernel(x_test + i * d, x_train + j * d, d, gamma)
+                            : oracle_device_kernel(t32 + i * d, s32 + k * d, d, gamma);
+            curr += alpha[j] * y_train[j] * kv;
+        }
+        if (scores) scores[i] = curr;
+        int pred = ge_zero ? (curr >= 0 ? 1 : -1) : (curr > 0 ? 1 : -1);
+        if (pred == y_test[i]) ++correct;
+    }
+    free(t32); free(s32);
+    return correct;
+}

@@ -1,0 +1,108 @@
+/*
+ * oracle/smo_oracle.h -- CPU restatement of the reference's RBF-kernel SMO path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product: only
+ * tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load this library, and there only as the checker or the timed CPU arm.
+ *
+ * Every function cites the reference file:line it follows (paths relative to the
+ * upstream repository root, e.g. code/main3.cpp:92).  Parity of this restatement
+ * is pinned by tests/test_oracle.py against oracle/_ref (the unmodified
+ * code/main3.cpp compiled through oracle/ref_wrapper.cpp) and against the golden
+ * fixtures under tests/golden/ that were generated from that build.
+ */
+#ifndef SMO_ORACLE_H
+#define SMO_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Literals of code/main3.cpp turned into parameters (defaults = those literals):
+ * C=10 (:163,:342) gamma=0.00125 (:95) eps=1e-12 (:109,:128,:165) tau=1e-5 (:196)
+ * max_iter=100000 (:198) sv_tol=1e-8 (:297,:367). */
+typedef struct {
+    double C;
+    double gamma;
+    double eps;
+    double tau;
+    int    max_iter;
+    double sv_tol;
+} oracle_params;
+
+/* stop_reason mirrors the reference's loop exits (code/main3.cpp:205,213,246,253,283) */
+enum {
+    ORACLE_STOP_CONVERGED  = 0, /* b_low <= b_high + 2 tau            :213 */
+    ORACLE_STOP_NOT_FOUND  = 1, /* i_high or i_low not found          :205 */
+    ORACLE_STOP_INFEASIBLE = 2, /* infeasible U and V                 :246 */
+    ORACLE_STOP_ETA        = 3, /* non positive eta                   :253 */
+    ORACLE_STOP_MAX_ITER   = 4  /* num_iter > max_iter                :283 */
+};
+
+/* how kernel rows are evaluated */
+enum {
+    ORACLE_ARITH_F64      = 0, /* the reference's arithmetic: sequential FP64 sum, libm exp */
+    ORACLE_ARITH_DEVICE   = 1  /* the CUDA path's arithmetic restated op for op (fp32 X,
+                                  float4-chunk fp32 partial sums, FP64 lane sums, fixed
+                                  butterfly order, svm_exp): used to check the GPU bit for bit */
+};
+
+typedef struct {
+    int      num_iter;     /* the reference's printed counter: starts at 1, +1 per update (:197,:281) */
+    int      stop_reason;
+    int64_t  i_high, i_low;   /* last selected pair */
+    double   b_high, b_low;
+    int64_t  rows_computed;   /* kernel rows evaluated (1-row reuse counted, :216-232) */
+} oracle_result;
+
+void   oracle_default_params(oracle_params *p);
+
+/* code/main3.cpp:92-104 with gamma as a parameter */
+double oracle_kernel(const double *v1, const double *v2, size_t d, double gamma);
+/* code/main3.cpp:57-71 and :74-89 */
+void   oracle_find_min_max(const double *x, double *min_val, double *max_val, size_t n, size_t d);
+void   oracle_scale_features(double *x, const double *min_val, const double *max_val, size_t n, size_t d);
+/* code/main3.cpp:107-123, :126-142 -- return n when the set is empty */
+size_t oracle_calc_i_high(const double *alpha, const int *y, const double *f, size_t n, double C, double eps);
+size_t oracle_calc_i_low(const double *alpha, const int *y, const double *f, size_t n, double C, double eps);
+/* code/main3.cpp:145-159 */
+int    oracle_calculate_U_V(int s, double a_high, double a_low, double C, double *U, double *V);
+
+/* code/main3.cpp:162-294 (init != 0) and code/mpi_svm_main2.cpp:154-288 (init == 0: alpha is
+ * in/out and f is rebuilt from it, :167-183).  trace (optional) receives (i_high, i_low) of every
+ * iteration that reached the update, trace_cap pairs at most.  f_out (optional) receives the final
+ * error vector.  arith selects ORACLE_ARITH_*.  Returns 0. */
+int    oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
+                        double *alpha, double *b, const oracle_params *p, int init,
+                        int arith, oracle_result *res,
+                        int32_t *trace, size_t trace_cap, double *f_out);
+
+/* code/main3.cpp:297-304: ascending indices with alpha > tol; returns the count */
+size_t oracle_sv_indices(const double *alpha, size_t n, double tol, int32_t *idx);
+
+/* code/main3.cpp:391-405 (ge_zero == 0: curr > 0) and code/mpi_svm_main2.cpp:721-733
+ * (ge_zero != 0: s >= 0).  SV rows given by sv_idx into x_train.  scores (optional) gets the
+ * decision values.  Returns the number of correct predictions. */
+int    oracle_predict(const double *x_test, const int *y_test, size_t m,
+                      const double *x_train, const int *y_train, const double *alpha,
+                      const int32_t *sv_idx, size_t n_sv, size_t d, double gamma, double b,
+                      int ge_zero, int arith, double *scores);
+
+/* ---- the CUDA path's arithmetic, restated (ORACLE_ARITH_DEVICE) ---- */
+/* exp() restated with IEEE +,*,fma only, so host and device agree bit for bit */
+double oracle_device_exp(double x);
+/* fp32 squares summed before widening to FP64 (svmb200_params.accum_chunk): 1 (default), 2 or 4 */
+void   oracle_set_device_chunk(int ch);
+int    oracle_get_device_chunk(void);
+/* squared distance of two fp32 rows: fp32 differences, fp32 fma over each float4, FP64 lane
+ * sums over lanes l = q mod 32, xor-butterfly 16,8,4,2,1 */
+double oracle_device_sqdist(const float *a, const float *b, size_t d);
+double oracle_device_kernel(const float *a, const float *b, size_t d, double gamma);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

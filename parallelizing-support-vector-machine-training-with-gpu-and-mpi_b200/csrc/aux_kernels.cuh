@@ -1,0 +1,245 @@
+// aux_kernels.cuh -- the kernels either side of the SMO loop: ingest/scale, state init, the batched
+// decision function (prediction and warm-start f), and the small introspection kernels.
+#pragma once
+#include "device_math.cuh"
+#include "smo_kernel.cuh"
+
+namespace svm {
+
+// ---- per-feature min/max: replaces find_min_max (code/main3.cpp:57-71) and the reference GPU's
+// four full-size scratch copies + 4 passes (code/gpu_svm_main3.cu:540-572).  One read of X:
+// CTA b scans rows [b*rows_per_cta, ...) with thread c on column c, then a second tiny kernel
+// folds the per-CTA partials.  Scratch: 2 * gridDim.x * d doubles.
+template <typename T>
+__global__ void colminmax_partial_kernel(const T *__restrict__ X, long long n, int d, int rows_per_cta,
+                                         double *__restrict__ pmin, double *__restrict__ pmax)
+{
+    const long long r0 = (long long)blockIdx.x * rows_per_cta;
+    const long long r1 = min(n, r0 + rows_per_cta);
+    for (int c = threadIdx.x; c < d; c += blockDim.x) {
+        double lo = __longlong_as_double(0x7ff0000000000000LL), hi = __longlong_as_double(0xfff0000000000000LL);
+        for (long long r = r0; r < r1; ++r) {
+            const double v = (double)X[r * d + c];
+            lo = v < lo ? v : lo;
+            hi = hi < v ? v : hi;
+        }
+        pmin[(size_t)blockIdx.x * d + c] = lo;
+        pmax[(size_t)blockIdx.x * d + c] = hi;
+    }
+}
+
+__global__ void colminmax_final_kernel(const double *__restrict__ pmin, const double *__restrict__ pmax, int parts, int d,
+                                       double *__restrict__ minv, double *__restrict__ maxv)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= d) return;
+    double lo = pmin[c], hi = pmax[c];
+    for (int p = 1; p < parts; ++p) {
+        const double a = pmin[(size_t)p * d + c], b = pmax[(size_t)p * d + c];
+        lo = a < lo ? a : lo;
+        hi = hi < b ? b : hi;
+    }
+    minv[c] = lo;
+    maxv[c] = hi;
+}
+
+// ---- scale + narrow + pad: replaces scale_features (code/main3.cpp:74-89): (x - min) / range in
+// FP64 with range < 1e-12 -> 1, then rounded once to fp32.  minv == nullptr: X is already scaled.
+template <typename T>
+__global__ void scale_to_f32_kernel(const T *__restrict__ X, long long n, int d, int pitch4,
+                                    const double *__restrict__ minv, const double *__restrict__ maxv,
+                                    float *__restrict__ out)
+{
+    const long long total = n * pitch4;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+        const long long r = g / pitch4;
+        const int q = (int)(g - r * pitch4);
+        float v[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int col = 4 * q + c;
+            double x = 0.0;
+            if (col < d) {
+                x = (double)X[r * d + col];
+                if (minv) {
+                    double range = maxv[col] - minv[col];
+                    if (range < 1e-12) range = 1.0;
+                    x = (x - minv[col]) / range;
+                }
+            }
+            v[c] = (float)x;
+        }
+        reinterpret_cast<float4 *>(out)[g] = make_float4(v[0], v[1], v[2], v[3]);
+    }
+}
+
+// ---- solver state init: alpha = 0, f = -y (code/main3.cpp:167-172; gpu_svm_main3.cu:152-161)
+__global__ void init_state_kernel(const int *__restrict__ y, long long n, double *__restrict__ f, double *__restrict__ alpha,
+                                  long long *__restrict__ cacheq, int zero_alpha, int set_f)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        if (zero_alpha) alpha[i] = 0.0;
+        if (set_f) f[i] = -(double)y[i];
+        if (cacheq) cacheq[i] = -1;
+    }
+}
+
+// ---- gather rows (support vectors) into a dense block
+__global__ void gather_rows_kernel(const float *__restrict__ X, int pitch4, const int *__restrict__ ids, int count,
+                                   float *__restrict__ out)
+{
+    const long long total = (long long)count * pitch4;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+        const long long k = g / pitch4;
+        const int q = (int)(g - k * pitch4);
+        reinterpret_cast<float4 *>(out)[g] = reinterpret_cast<const float4 *>(X)[(size_t)ids[k] * pitch4 + q];
+    }
+}
+
+// ---- batched decision function: replaces the prediction loop (code/main3.cpp:391-402), the
+// reference GPU's predict kernel (gpu_svm_main3.cu:277-293, which loops over ALL n rows) and the
+// warm-start f rebuild (code/mpi_svm_main2.cpp:169-183).
+//   out[i] = init + sum_k coef[k] * K(q_i, sv_k)   (k ascending, sequential FP64, as the reference)
+//   then, if ysub != nullptr, out[i] -= ysub[i]     (f_i = sum - y_i)
+// A warp owns one query row (registers); the CTA streams the support-vector block through shared
+// memory in tiles of DEC_TILE rows (bulk copies, double-buffered), every warp reading each tile.
+constexpr int DEC_THREADS = 512;
+constexpr int DEC_WARPS = DEC_THREADS / 32;
+constexpr int DEC_TILE = 16;
+
+template <int Q, int CH>
+__global__ void __launch_bounds__(DEC_THREADS, 1)
+decision_kernel(const float *__restrict__ Xq, long long m, const float *__restrict__ SV, const double *__restrict__ coef,
+                int nsv, int pitch4, double gamma, double init, const int *__restrict__ ysub, double *__restrict__ out)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row_bytes = pitch4 * 16;
+    unsigned char *tiles = smem_raw;                                   // [2][DEC_TILE][row_bytes]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(tiles + (size_t)2 * DEC_TILE * row_bytes);
+
+    if (threadIdx.x == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const long long qi = (long long)blockIdx.x * DEC_WARPS + warp;
+    const bool active = qi < m;
+    float4 qv[Q];
+#pragma unroll
+    for (int i = 0; i < Q; ++i) {
+        const int q = i * 32 + lane;
+        qv[i] = (active && q < pitch4) ? __ldg(reinterpret_cast<const float4 *>(Xq) + (size_t)qi * pitch4 + q)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+
+    const int ntiles = (nsv + DEC_TILE - 1) / DEC_TILE;
+    auto issue_tile = [&](int t) {      // thread 0
+        const int rows = min(DEC_TILE, nsv - t * DEC_TILE);
+        mbar_expect_tx(&bars[t & 1], (unsigned)(rows * row_bytes));
+        bulk_g2s(tiles + (size_t)(t & 1) * DEC_TILE * row_bytes, SV + (size_t)t * DEC_TILE * pitch4 * 4,
+                 (unsigned)(rows * row_bytes), &bars[t & 1], L2_EVICT_LAST);
+    };
+    if (threadIdx.x == 0 && ntiles > 0) issue_tile(0);
+
+    double sum = init;
+    for (int t = 0; t < ntiles; ++t) {
+        if (threadIdx.x == 0 && t + 1 < ntiles) issue_tile(t + 1);   // buffer (t+1)&1 was released by the barrier below
+        mbar_wait(&bars[t & 1], (t >> 1) & 1);
+        const int rows = min(DEC_TILE, nsv - t * DEC_TILE);
+        const unsigned char *tile = tiles + (size_t)(t & 1) * DEC_TILE * row_bytes;
+        double myk = 0.0;
+        for (int r = 0; r < rows; ++r) {
+            const float4 *row = reinterpret_cast<const float4 *>(tile + (size_t)r * row_bytes);
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) {
+                const int q = i * 32 + lane;
+                if (q < pitch4) accum_sq<CH>(row[q], qv[i], acc);
+            }
+            acc = warp_sum_butterfly(acc);
+            if (lane == r) myk = acc;
+        }
+        myk = svm_exp(-gamma * myk);                                  // lanes >= rows compute a value nobody reads
+        const double mycoef = lane < rows ? coef[t * DEC_TILE + lane] : 0.0;
+        for (int r = 0; r < rows; ++r) {
+            const double k = __shfl_sync(FULL, myk, r);
+            const double c = __shfl_sync(FULL, mycoef, r);
+            sum = sum + c * k;                                        // curr += alpha[j]*y[j] * kernel(...)
+        }
+        fence_proxy_async();
+        __syncthreads();                                              // everyone is done with buffer t&1
+    }
+    if (active && lane == 0) {
+        if (ysub) sum = sum - (double)ysub[qi];
+        out[qi] = sum;
+    }
+}
+
+inline size_t decision_smem_bytes(int pitch4) { return (size_t)2 * DEC_TILE * pitch4 * 16 + 64; }
+
+// ---- accuracy: replaces the predict/compare/reduce_sum tail (code/main3.cpp:399-401;
+// gpu_svm_main3.cu:291,299-315): "> 0" (serial/GPU) or ">= 0" (MPI programs)
+__global__ void count_correct_kernel(const double *__restrict__ scores, const int *__restrict__ y, long long m, int ge_zero,
+                                     int *__restrict__ correct)
+{
+    int c = 0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x) {
+        const int pred = ge_zero ? (scores[i] >= 0 ? 1 : -1) : (scores[i] > 0 ? 1 : -1);
+        c += pred == y[i];
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) c += __shfl_xor_sync(FULL, c, off);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(correct, c);
+}
+
+// ---- introspection: one kernel row exactly as the solver forms it (a warp per row, no staging)
+template <int Q, int CH>
+__global__ void kernel_row_kernel(const float *__restrict__ X, long long n, int pitch4, long long pivot, double gamma,
+                                  double *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (j >= n) return;
+    const float4 *xp = reinterpret_cast<const float4 *>(X) + (size_t)pivot * pitch4;
+    const float4 *xj = reinterpret_cast<const float4 *>(X) + (size_t)j * pitch4;
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < Q; ++i) {
+        const int q = i * 32 + lane;
+        if (q < pitch4) accum_sq<CH>(__ldg(xj + q), __ldg(xp + q), acc);
+    }
+    acc = warp_sum_butterfly(acc);
+    if (lane == 0) out[j] = svm_exp(-gamma * acc);
+}
+
+// ---- introspection: one working-set selection with the solver's own compare (single CTA)
+__global__ void select_pair_kernel(const double *__restrict__ alpha, const double *__restrict__ f, const int *__restrict__ y,
+                                   long long n, double C, double eps, long long *__restrict__ out)
+{
+    __shared__ double sfmin[32], sfmax[32];
+    __shared__ int simin[32], simax[32];
+    LocalBest b;
+    best_init(b);
+    for (long long j = threadIdx.x; j < n; j += blockDim.x) {
+        if (in_I_high(y[j], alpha[j], C, eps) && f[j] < b.fmin) { b.fmin = f[j]; b.imin = (int)j; }
+        if (in_I_low(y[j], alpha[j], C, eps) && f[j] > b.fmax) { b.fmax = f[j]; b.imax = (int)j; }
+    }
+    best_warp_reduce(b);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sfmin[warp] = b.fmin; simin[warp] = b.imin; sfmax[warp] = b.fmax; simax[warp] = b.imax; }
+    __syncthreads();
+    if (warp == 0) {
+        best_init(b);
+        if (lane < (int)(blockDim.x >> 5)) { b.fmin = sfmin[lane]; b.imin = simin[lane]; b.fmax = sfmax[lane]; b.imax = simax[lane]; }
+        best_warp_reduce(b);
+        if (lane == 0) {
+            out[0] = b.imin == IDX_NONE ? n : b.imin;
+            out[1] = b.imax == IDX_NONE ? n : b.imax;
+        }
+    }
+}
+
+} // namespace svm

@@ -1,0 +1,696 @@
+// capi.cu -- the C ABI of include/svmb200.h over the CUDA kernels (sm_100a only).
+//
+// Host-side control only: buffer management, launches, the D2H copies of results.  There is no
+// CPU implementation of any step here; if CUDA is unavailable every entry point fails loudly.
+#include "../../include/svmb200.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "aux_kernels.cuh"
+#include "smo_kernel.cuh"
+
+using namespace svm;
+
+static thread_local std::string g_create_error;
+
+struct svmb200_ctx {
+    int device = 0;
+    int num_sms = 0;
+    int max_smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    std::string err;
+
+    // training set
+    long long n = 0;
+    int d = 0, pitch4 = 0;
+    float *X = nullptr;
+    int *y = nullptr;
+    double *minv = nullptr, *maxv = nullptr;
+    bool have_stats = false, have_train = false;
+
+    // solver state
+    double *f = nullptr, *alpha = nullptr;
+    long long *cacheq = nullptr;
+    double *cacheK = nullptr;
+    long long cacheK_rows = 0;
+    Rec *rec = nullptr;
+    int rec_blocks = 0;
+    SmoResult *result = nullptr;
+    int *trace = nullptr;
+    int trace_alloc = 0, trace_count = 0;
+
+    // model
+    bool trained = false;
+    svmb200_params params{};
+    double b = 0.0;
+    std::vector<double> alpha_host;
+    std::vector<int> sv_ids;
+    float *svX = nullptr;
+    double *svcoef = nullptr;
+    int sv_alloc = 0;
+
+    // generic scratch
+    void *scratch = nullptr;
+    size_t scratch_bytes = 0;
+    int launches = 0;
+};
+
+#define CK(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) {                                                                        \
+            char buf_[512];                                                                             \
+            snprintf(buf_, sizeof buf_, "%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+            ctx->err = buf_;                                                                            \
+            return SVMB200_ECUDA;                                                                       \
+        }                                                                                               \
+    } while (0)
+
+#define FAIL(code, ...)                                  \
+    do {                                                 \
+        char buf_[512];                                  \
+        snprintf(buf_, sizeof buf_, __VA_ARGS__);        \
+        ctx->err = buf_;                                 \
+        return (code);                                   \
+    } while (0)
+
+static int ensure_scratch(svmb200_ctx *ctx, size_t bytes)
+{
+    if (bytes <= ctx->scratch_bytes) return 0;
+    if (ctx->scratch) CK(cudaFree(ctx->scratch));
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+    CK(cudaMalloc(&ctx->scratch, bytes));
+    ctx->scratch_bytes = bytes;
+    return 0;
+}
+
+template <typename T>
+static int dev_free(svmb200_ctx *ctx, T *&p)
+{
+    if (p) CK(cudaFree(p));
+    p = nullptr;
+    return 0;
+}
+
+extern "C" {
+
+const char *svmb200_version(void) { return "svmb200 0.1 (sm_100a)"; }
+
+void svmb200_default_params(svmb200_params *p)
+{
+    p->C = 10.0;            // main3.cpp:163,342
+    p->gamma = 0.00125;     // main3.cpp:95
+    p->eps = 1e-12;         // main3.cpp:165
+    p->tau = 1e-5;          // main3.cpp:196
+    p->max_iter = 100000;   // main3.cpp:198
+    p->sv_tol = 1e-8;       // main3.cpp:367
+    p->wss = 1;
+    p->warm_start = 0;
+    p->cache_rows = 0;
+    p->accum_chunk = 0;
+    p->trace_cap = 0;
+    p->l2_persist = 0;
+}
+
+const char *svmb200_last_error(const svmb200_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int svmb200_create(svmb200_ctx **out, int device)
+{
+    if (!out) return SVMB200_EINVAL;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e);
+        return SVMB200_ENODEVICE;
+    }
+    if (device < 0 || device >= count) {
+        g_create_error = "device ordinal out of range";
+        return SVMB200_EINVAL;
+    }
+    svmb200_ctx *ctx = new svmb200_ctx();
+    ctx->device = device;
+    auto fail = [&](const char *what, cudaError_t err) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+        delete ctx;
+        return SVMB200_ECUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
+    if (prop.major != 10) {
+        g_create_error = "svmb200 is built for sm_100a only; device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor);
+        delete ctx;
+        return SVMB200_ENODEVICE;
+    }
+    ctx->num_sms = prop.multiProcessorCount;
+    ctx->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev0)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev2)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaMalloc(&ctx->result, sizeof(SmoResult))) != cudaSuccess) return fail("cudaMalloc", e);
+    *out = ctx;
+    return SVMB200_OK;
+}
+
+void svmb200_destroy(svmb200_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->X); cudaFree(ctx->y); cudaFree(ctx->minv); cudaFree(ctx->maxv);
+    cudaFree(ctx->f); cudaFree(ctx->alpha); cudaFree(ctx->cacheq); cudaFree(ctx->cacheK);
+    cudaFree(ctx->rec); cudaFree(ctx->result); cudaFree(ctx->trace);
+    cudaFree(ctx->svX); cudaFree(ctx->svcoef); cudaFree(ctx->scratch);
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev2);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------
+static int alloc_train(svmb200_ctx *ctx, long long n, int d)
+{
+    if (n <= 0 || d <= 0) FAIL(SVMB200_EINVAL, "n and d must be positive (n=%lld d=%d)", n, d);
+    if (n >= 0x7fffffffLL) FAIL(SVMB200_ELIMIT, "n=%lld exceeds the 2^31-2 row limit", n);
+    const int pitch4 = (d + 3) / 4;
+    if (pitch4 > 256) FAIL(SVMB200_ELIMIT, "d=%d exceeds the 1024-feature limit of the in-register pivot rows", d);
+    CK(cudaSetDevice(ctx->device));
+    if (n != ctx->n || d != ctx->d) {
+        if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
+            dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv))
+            return SVMB200_ECUDA;
+        CK(cudaMalloc(&ctx->X, (size_t)n * pitch4 * 16));
+        CK(cudaMalloc(&ctx->y, (size_t)n * sizeof(int)));
+        CK(cudaMalloc(&ctx->f, (size_t)n * sizeof(double)));
+        CK(cudaMalloc(&ctx->alpha, (size_t)n * sizeof(double)));
+        CK(cudaMalloc(&ctx->cacheq, (size_t)n * sizeof(long long)));
+        CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
+        CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
+        ctx->n = n;
+        ctx->d = d;
+        ctx->pitch4 = pitch4;
+    }
+    ctx->have_train = false;
+    ctx->trained = false;
+    ctx->have_stats = false;
+    return 0;
+}
+
+// stage raw host rows in device scratch, compute statistics (optional), scale into dst
+template <typename T>
+static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool compute_stats, bool apply_stats, float *dst)
+{
+    const int d = ctx->d, pitch4 = ctx->pitch4;
+    const size_t raw_bytes = (size_t)rows * d * sizeof(T);
+    const int parts = (int)std::min<long long>(ctx->num_sms * 4, (rows + 63) / 64);
+    const size_t part_bytes = compute_stats ? (size_t)2 * parts * d * sizeof(double) : 0;
+    const size_t raw_off = (part_bytes + 255) & ~(size_t)255;
+    if (int rc = ensure_scratch(ctx, raw_off + raw_bytes)) return rc;
+    T *raw = reinterpret_cast<T *>(static_cast<char *>(ctx->scratch) + raw_off);
+    CK(cudaMemcpyAsync(raw, X_host, raw_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (compute_stats) {
+        double *pmin = static_cast<double *>(ctx->scratch), *pmax = pmin + (size_t)parts * d;
+        const int rows_per_cta = (int)((rows + parts - 1) / parts);
+        colminmax_partial_kernel<T><<<parts, 256, 0, ctx->stream>>>(raw, rows, d, rows_per_cta, pmin, pmax);
+        colminmax_final_kernel<<<(d + 127) / 128, 128, 0, ctx->stream>>>(pmin, pmax, parts, d, ctx->minv, ctx->maxv);
+        ctx->launches += 2;
+        CK(cudaGetLastError());
+    }
+    const long long total = rows * pitch4;
+    const int blocks = (int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16);
+    scale_to_f32_kernel<T><<<blocks, 256, 0, ctx->stream>>>(raw, rows, d, pitch4, apply_stats ? ctx->minv : nullptr,
+                                                            apply_stats ? ctx->maxv : nullptr, dst);
+    ctx->launches += 1;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+template <typename T>
+static int set_train(svmb200_ctx *ctx, const T *X, const int32_t *y, int64_t n, int32_t d, bool scale, double *min_out,
+                     double *max_out)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!X || !y) FAIL(SVMB200_EINVAL, "X and y must not be NULL");
+    if (int rc = alloc_train(ctx, n, d)) return rc;
+    if (int rc = ingest<T>(ctx, X, n, scale, scale, ctx->X)) return rc;
+    CK(cudaMemcpyAsync(ctx->y, y, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    if (scale) {
+        if (min_out) CK(cudaMemcpyAsync(min_out, ctx->minv, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+        if (max_out) CK(cudaMemcpyAsync(max_out, ctx->maxv, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->have_stats = scale;
+    ctx->have_train = true;
+    return SVMB200_OK;
+}
+
+extern "C" {
+
+int svmb200_set_train_u8(svmb200_ctx *ctx, const uint8_t *X, const int32_t *y, int64_t n, int32_t d, double *min_out, double *max_out)
+{
+    return set_train<uint8_t>(ctx, X, y, n, d, true, min_out, max_out);
+}
+int svmb200_set_train_f64(svmb200_ctx *ctx, const double *X, const int32_t *y, int64_t n, int32_t d, double *min_out, double *max_out)
+{
+    return set_train<double>(ctx, X, y, n, d, true, min_out, max_out);
+}
+int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y, int64_t n, int32_t d)
+{
+    return set_train<double>(ctx, Xs, y, n, d, false, nullptr, nullptr);
+}
+
+} // extern "C"
+
+// ------------------------------------------------------------------------------------------
+static int q_for_pitch(int pitch4)
+{
+    const int need = (pitch4 + 31) / 32;
+    if (need <= 1) return 1;
+    if (need <= 2) return 2;
+    if (need <= 4) return 4;
+    if (need <= 7) return need == 7 ? 7 : 8;
+    return 8;
+}
+
+template <int Q, int CH>
+static cudaError_t launch_smo(const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+{
+    cudaError_t e = cudaFuncSetAttribute(smo_persistent_kernel<Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    void *kargs[] = {(void *)&args};
+    return cudaLaunchCooperativeKernel((void *)smo_persistent_kernel<Q, CH>, dim3(grid), dim3(SMO_THREADS), kargs, smem, stream);
+}
+
+template <int CH>
+static cudaError_t launch_smo_q(int Q, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+{
+    switch (Q) {
+    case 1: return launch_smo<1, CH>(args, grid, smem, stream);
+    case 2: return launch_smo<2, CH>(args, grid, smem, stream);
+    case 4: return launch_smo<4, CH>(args, grid, smem, stream);
+    case 7: return launch_smo<7, CH>(args, grid, smem, stream);
+    default: return launch_smo<8, CH>(args, grid, smem, stream);
+    }
+}
+
+static cudaError_t launch_smo_any(int Q, int CH, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+{
+    switch (CH) {
+    case 1: return launch_smo_q<1>(Q, args, grid, smem, stream);
+    case 2: return launch_smo_q<2>(Q, args, grid, smem, stream);
+    default: return launch_smo_q<4>(Q, args, grid, smem, stream);
+    }
+}
+
+template <int Q, int CH>
+static cudaError_t launch_decision(const float *Xq, long long m, const float *SV, const double *coef, int nsv, int pitch4,
+                                   double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
+{
+    const size_t smem = decision_smem_bytes(pitch4);
+    cudaError_t e = cudaFuncSetAttribute(decision_kernel<Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int grid = (int)((m + DEC_WARPS - 1) / DEC_WARPS);
+    decision_kernel<Q, CH><<<grid, DEC_THREADS, smem, stream>>>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out);
+    return cudaGetLastError();
+}
+
+template <int CH>
+static cudaError_t launch_decision_q(int Q, const float *Xq, long long m, const float *SV, const double *coef, int nsv,
+                                     int pitch4, double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
+{
+    switch (Q) {
+    case 1: return launch_decision<1, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 2: return launch_decision<2, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 4: return launch_decision<4, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 7: return launch_decision<7, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    default: return launch_decision<8, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    }
+}
+
+static cudaError_t launch_decision_any(int Q, int CH, const float *Xq, long long m, const float *SV, const double *coef,
+                                       int nsv, int pitch4, double gamma, double init, const int *ysub, double *out,
+                                       cudaStream_t stream)
+{
+    switch (CH) {
+    case 1: return launch_decision_q<1>(Q, Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 2: return launch_decision_q<2>(Q, Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    default: return launch_decision_q<4>(Q, Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    }
+}
+
+template <int Q, int CH>
+static cudaError_t launch_krow(const float *X, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
+{
+    const long long threads = n * 32;
+    kernel_row_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, n, pitch4, pivot, gamma, out);
+    return cudaGetLastError();
+}
+template <int CH>
+static cudaError_t launch_krow_q(int Q, const float *X, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
+{
+    switch (Q) {
+    case 1: return launch_krow<1, CH>(X, n, pitch4, pivot, gamma, out, s);
+    case 2: return launch_krow<2, CH>(X, n, pitch4, pivot, gamma, out, s);
+    case 4: return launch_krow<4, CH>(X, n, pitch4, pivot, gamma, out, s);
+    case 7: return launch_krow<7, CH>(X, n, pitch4, pivot, gamma, out, s);
+    default: return launch_krow<8, CH>(X, n, pitch4, pivot, gamma, out, s);
+    }
+}
+
+static const int DEFAULT_CHUNK = 1;
+
+static int resolve_chunk(int c)
+{
+    if (c == 0) return DEFAULT_CHUNK;
+    return (c == 1 || c == 2 || c == 4) ? c : -1;
+}
+
+// coefficients alpha_j * y_j and the dense SV block for the decision kernel
+static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const double *alpha_host, const std::vector<int> &y_host_sv)
+{
+    const int nsv = (int)ids.size();
+    if (nsv > ctx->sv_alloc) {
+        if (dev_free(ctx, ctx->svX) || dev_free(ctx, ctx->svcoef)) return SVMB200_ECUDA;
+        const int cap = std::max(nsv, 1024);
+        CK(cudaMalloc(&ctx->svX, (size_t)cap * ctx->pitch4 * 16));
+        CK(cudaMalloc(&ctx->svcoef, (size_t)cap * sizeof(double)));
+        ctx->sv_alloc = cap;
+    }
+    if (nsv == 0) return 0;
+    std::vector<double> coef(nsv);
+    for (int k = 0; k < nsv; ++k) coef[k] = alpha_host[ids[k]] * y_host_sv[k];   // alpha[j] * y_train[j]
+    if (int rc = ensure_scratch(ctx, (size_t)nsv * sizeof(int))) return rc;
+    CK(cudaMemcpyAsync(ctx->scratch, ids.data(), (size_t)nsv * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->svcoef, coef.data(), (size_t)nsv * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    const long long total = (long long)nsv * ctx->pitch4;
+    gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+        ctx->X, ctx->pitch4, static_cast<const int *>(ctx->scratch), nsv, ctx->svX);
+    ctx->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));   // coef / ids are host temporaries
+    return 0;
+}
+
+extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params, double *alpha, double *b, svmb200_stats *stats)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!params || !alpha || !b) FAIL(SVMB200_EINVAL, "params, alpha and b must not be NULL");
+    if (!ctx->have_train) FAIL(SVMB200_ESTATE, "svmb200_smo_train called before svmb200_set_train_*");
+    if (params->wss != 1) FAIL(SVMB200_EINVAL, "wss=%d: only the reference's first-order rule (1) exists", params->wss);
+    const int CH = resolve_chunk(params->accum_chunk);
+    if (CH < 0) FAIL(SVMB200_EINVAL, "accum_chunk must be 0, 1, 2 or 4");
+    if (params->max_iter < 1) FAIL(SVMB200_EINVAL, "max_iter must be >= 1");
+    CK(cudaSetDevice(ctx->device));
+    const long long n = ctx->n;
+    const int launches0 = ctx->launches;
+
+    // persistent grid: one CTA per SM, fewer for tiny problems
+    const int Q = q_for_pitch(ctx->pitch4);
+    int kslots = SMO_KSLOTS_MAX;
+    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots) > (size_t)ctx->max_smem_optin) --kslots;
+    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots);
+    if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
+    const int grid = (int)std::max<long long>(1, std::min<long long>(ctx->num_sms, (n + 7) / 8));
+
+    // row cache
+    int cache_cap = params->cache_rows;
+    if (cache_cap < 0) {
+        const size_t budget = (size_t)8 << 30;
+        cache_cap = (int)std::min<long long>(n, (long long)(budget / ((size_t)n * sizeof(double))));
+    }
+    if (cache_cap == 1) cache_cap = 2;
+    if (cache_cap > 0 && (long long)cache_cap != ctx->cacheK_rows) {
+        if (dev_free(ctx, ctx->cacheK)) return SVMB200_ECUDA;
+        ctx->cacheK_rows = 0;
+        CK(cudaMalloc(&ctx->cacheK, (size_t)cache_cap * n * sizeof(double)));
+        ctx->cacheK_rows = cache_cap;
+    }
+
+    if (grid > ctx->rec_blocks) {
+        if (dev_free(ctx, ctx->rec)) return SVMB200_ECUDA;
+        CK(cudaMalloc(&ctx->rec, (size_t)2 * grid * sizeof(Rec)));
+        ctx->rec_blocks = grid;
+    }
+    const int trace_cap = std::max(0, params->trace_cap);
+    if (trace_cap > ctx->trace_alloc) {
+        if (dev_free(ctx, ctx->trace)) return SVMB200_ECUDA;
+        CK(cudaMalloc(&ctx->trace, (size_t)trace_cap * 2 * sizeof(int)));
+        ctx->trace_alloc = trace_cap;
+    }
+
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    CK(cudaMemsetAsync(ctx->rec, 0, (size_t)2 * ctx->rec_blocks * sizeof(Rec), ctx->stream));
+    if (params->warm_start) {
+        // f_i = sum_{alpha_j != 0} alpha_j y_j K(x_j, x_i) - y_i   (mpi_svm_main2.cpp:169-183)
+        CK(cudaMemcpyAsync(ctx->alpha, alpha, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        std::vector<int> y_host(n);
+        CK(cudaMemcpyAsync(y_host.data(), ctx->y, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        std::vector<int> nz, nzy;
+        for (long long j = 0; j < n; ++j)
+            if (alpha[j] != 0.0) { nz.push_back((int)j); nzy.push_back(y_host[j]); }
+        if (int rc = build_sv_block(ctx, nz, alpha, nzy)) return rc;
+        init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 0, 0);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+        CK(launch_decision_any(Q, CH, ctx->X, n, ctx->svX, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
+                               ctx->y, ctx->f, ctx->stream));
+        ctx->launches += 1;
+    } else {
+        init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 1, 1);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+    }
+
+    SmoArgs a{};
+    a.X = ctx->X; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
+    a.cacheq = cache_cap > 0 ? ctx->cacheq : nullptr;
+    a.cacheK = ctx->cacheK; a.rec = ctx->rec; a.trace = ctx->trace; a.result = ctx->result;
+    a.n = n; a.pitch4 = ctx->pitch4; a.kslots = kslots; a.cache_cap = cache_cap; a.trace_cap = trace_cap;
+    a.max_iter = params->max_iter;
+    a.C = params->C; a.gamma = params->gamma; a.eps = params->eps; a.tau = params->tau;
+    a.policy_stream = L2_EVICT_FIRST; a.policy_keep = L2_EVICT_LAST; a.keep_per_1024 = 0;
+    {
+        // L2 residency: when X does not fit in L2, keep a leading share of every warp's rows
+        const double x_bytes = (double)n * ctx->pitch4 * 16;
+        const double l2_keep_budget = 96.0 * 1024 * 1024;
+        int persist = params->l2_persist;
+        if (persist < 0) persist = 1;
+        if (x_bytes <= l2_keep_budget) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
+        else if (persist) a.keep_per_1024 = (int)(1024.0 * l2_keep_budget / x_bytes);
+    }
+    a.peers = 1; a.rank = 0; a.row_begin = 0; a.row_end = n; a.mailbox = nullptr;
+
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    CK(launch_smo_any(Q, CH, a, grid, smem, ctx->stream));
+    ctx->launches += 1;
+    CK(cudaEventRecord(ctx->ev2, ctx->stream));
+
+    SmoResult r;
+    CK(cudaMemcpyAsync(&r, ctx->result, sizeof r, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(alpha, ctx->alpha, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+
+    *b = (r.b_high + r.b_low) / 2;   // main3.cpp:291
+    ctx->b = *b;
+    ctx->params = *params;
+    ctx->params.accum_chunk = CH;
+    ctx->alpha_host.assign(alpha, alpha + n);
+    ctx->sv_ids.clear();
+    for (long long i = 0; i < n; ++i)            // get_SV_indices, main3.cpp:297-304
+        if (alpha[i] > params->sv_tol) ctx->sv_ids.push_back((int)i);
+    ctx->trace_count = std::min(trace_cap, r.num_iter - 1);
+    ctx->trained = true;
+
+    if (stats) {
+        float ms_init = 0.f, ms_smo = 0.f;
+        CK(cudaEventElapsedTime(&ms_init, ctx->ev0, ctx->ev1));
+        CK(cudaEventElapsedTime(&ms_smo, ctx->ev1, ctx->ev2));
+        stats->num_iter = r.num_iter;
+        stats->stop_reason = r.stop_reason;
+        stats->i_high = r.i_high;
+        stats->i_low = r.i_low;
+        stats->b_high = r.b_high;
+        stats->b_low = r.b_low;
+        stats->smo_ms = ms_smo;
+        stats->init_ms = ms_init;
+        stats->x_passes = r.x_passes;
+        stats->cache_hits = r.cache_hits;
+        stats->x_bytes_streamed = r.x_passes * n * (long long)ctx->pitch4 * 16;
+        stats->n_sv = (int)ctx->sv_ids.size();
+        stats->grid_blocks = grid;
+        stats->launches = ctx->launches - launches0;
+    }
+    return SVMB200_OK;
+}
+
+extern "C" int svmb200_sv_ids(svmb200_ctx *ctx, int32_t *ids, int32_t cap, int32_t *count)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!ctx->trained) FAIL(SVMB200_ESTATE, "svmb200_sv_ids called before svmb200_smo_train");
+    const int c = (int)ctx->sv_ids.size();
+    if (count) *count = c;
+    if (ids) {
+        if (cap < c) FAIL(SVMB200_EINVAL, "ids capacity %d < %d support vectors", cap, c);
+        memcpy(ids, ctx->sv_ids.data(), (size_t)c * sizeof(int));
+    }
+    return SVMB200_OK;
+}
+
+template <typename T>
+static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int64_t m, bool scale, int32_t ge_zero,
+                        int32_t *correct, double *scores)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!ctx->trained) FAIL(SVMB200_ESTATE, "svmb200_predict_* called before svmb200_smo_train");
+    if (!X || m <= 0) FAIL(SVMB200_EINVAL, "X must not be NULL and m must be positive");
+    if (scale && !ctx->have_stats) FAIL(SVMB200_ESTATE, "the training set was uploaded pre-scaled: use svmb200_predict_scaled_f64");
+    CK(cudaSetDevice(ctx->device));
+    const int pitch4 = ctx->pitch4;
+    // SV block (dense rows + coefficients)
+    std::vector<int> y_host(ctx->n);
+    CK(cudaMemcpyAsync(y_host.data(), ctx->y, (size_t)ctx->n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<int> svy(ctx->sv_ids.size());
+    for (size_t k = 0; k < svy.size(); ++k) svy[k] = y_host[ctx->sv_ids[k]];
+    if (int rc = build_sv_block(ctx, ctx->sv_ids, ctx->alpha_host.data(), svy)) return rc;
+
+    float *Xq = nullptr;
+    double *dscores = nullptr;
+    int *dy = nullptr, *dcorrect = nullptr;
+    CK(cudaMalloc(&Xq, (size_t)m * pitch4 * 16));
+    CK(cudaMalloc(&dscores, (size_t)m * sizeof(double)));
+    CK(cudaMalloc(&dy, (size_t)m * sizeof(int) + sizeof(int)));
+    dcorrect = dy + m;
+    int rc = ingest<T>(ctx, X, m, false, scale, Xq);
+    cudaError_t e = cudaSuccess;
+    if (!rc) {
+        e = launch_decision_any(q_for_pitch(pitch4), ctx->params.accum_chunk, Xq, m, ctx->svX, ctx->svcoef, (int)ctx->sv_ids.size(),
+                                pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores, ctx->stream);
+        ctx->launches += 1;
+    }
+    int host_correct = 0;
+    if (!rc && e == cudaSuccess && y_test) {
+        e = cudaMemcpyAsync(dy, y_test, (size_t)m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(dcorrect, 0, sizeof(int), ctx->stream);
+        if (e == cudaSuccess) {
+            count_correct_kernel<<<std::min<long long>((m + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(dscores, dy, m, ge_zero, dcorrect);
+            ctx->launches += 1;
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&host_correct, dcorrect, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (!rc && e == cudaSuccess && scores) e = cudaMemcpyAsync(scores, dscores, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(Xq); cudaFree(dscores); cudaFree(dy);
+    if (rc) return rc;
+    if (e != cudaSuccess) FAIL(SVMB200_ECUDA, "predict failed: %s", cudaGetErrorString(e));
+    if (correct) *correct = host_correct;
+    return SVMB200_OK;
+}
+
+extern "C" {
+
+int svmb200_predict_u8(svmb200_ctx *ctx, const uint8_t *X, const int32_t *y_test, int64_t m, int32_t ge_zero, int32_t *correct, double *scores)
+{
+    return predict_impl<uint8_t>(ctx, X, y_test, m, true, ge_zero, correct, scores);
+}
+int svmb200_predict_f64(svmb200_ctx *ctx, const double *X, const int32_t *y_test, int64_t m, int32_t ge_zero, int32_t *correct, double *scores)
+{
+    return predict_impl<double>(ctx, X, y_test, m, true, ge_zero, correct, scores);
+}
+int svmb200_predict_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y_test, int64_t m, int32_t ge_zero, int32_t *correct, double *scores)
+{
+    return predict_impl<double>(ctx, Xs, y_test, m, false, ge_zero, correct, scores);
+}
+
+int svmb200_get_trace(svmb200_ctx *ctx, int32_t *pairs, int32_t cap, int32_t *count)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!ctx->trained) FAIL(SVMB200_ESTATE, "no training run to trace");
+    const int c = std::min(cap, ctx->trace_count);
+    if (count) *count = c;
+    if (pairs && c > 0) {
+        CK(cudaSetDevice(ctx->device));
+        CK(cudaMemcpy(pairs, ctx->trace, (size_t)c * 2 * sizeof(int), cudaMemcpyDeviceToHost));
+    }
+    return SVMB200_OK;
+}
+
+int svmb200_get_f(svmb200_ctx *ctx, double *f)
+{
+    if (!ctx || !f) return SVMB200_EINVAL;
+    if (!ctx->trained) FAIL(SVMB200_ESTATE, "no training run");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(f, ctx->f, (size_t)ctx->n * sizeof(double), cudaMemcpyDeviceToHost));
+    return SVMB200_OK;
+}
+
+int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_chunk, double *row)
+{
+    if (!ctx || !row) return SVMB200_EINVAL;
+    if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set");
+    if (i < 0 || i >= ctx->n) FAIL(SVMB200_EINVAL, "row %lld out of range", (long long)i);
+    const int CH = resolve_chunk(accum_chunk);
+    if (CH < 0) FAIL(SVMB200_EINVAL, "accum_chunk must be 0, 1, 2 or 4");
+    CK(cudaSetDevice(ctx->device));
+    if (int rc = ensure_scratch(ctx, (size_t)ctx->n * sizeof(double))) return rc;
+    double *out = static_cast<double *>(ctx->scratch);
+    const int Q = q_for_pitch(ctx->pitch4);
+    cudaError_t e;
+    switch (CH) {
+    case 1: e = launch_krow_q<1>(Q, ctx->X, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
+    case 2: e = launch_krow_q<2>(Q, ctx->X, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
+    default: e = launch_krow_q<4>(Q, ctx->X, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
+    }
+    ctx->launches += 1;
+    CK(e);
+    CK(cudaMemcpyAsync(row, out, (size_t)ctx->n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SVMB200_OK;
+}
+
+int svmb200_select_pair(svmb200_ctx *ctx, const double *alpha, const double *f, const int32_t *y, int64_t n, double C,
+                        double eps, int64_t *i_high, int64_t *i_low)
+{
+    if (!ctx || !alpha || !f || !y || !i_high || !i_low || n <= 0) return SVMB200_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    const size_t need = (size_t)n * (2 * sizeof(double) + sizeof(int)) + 64;
+    if (int rc = ensure_scratch(ctx, need)) return rc;
+    double *da = static_cast<double *>(ctx->scratch), *df = da + n;
+    long long *dout = reinterpret_cast<long long *>(df + n);
+    int *dy = reinterpret_cast<int *>(dout + 2);
+    CK(cudaMemcpyAsync(da, alpha, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(df, f, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(dy, y, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    select_pair_kernel<<<1, 1024, 0, ctx->stream>>>(da, df, dy, n, C, eps, dout);
+    ctx->launches += 1;
+    CK(cudaGetLastError());
+    long long out[2];
+    CK(cudaMemcpyAsync(out, dout, sizeof out, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *i_high = out[0];
+    *i_low = out[1];
+    return SVMB200_OK;
+}
+
+int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs)
+{
+    if (!ctx || !Xs) return SVMB200_EINVAL;
+    if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy2D(Xs, (size_t)ctx->d * sizeof(float), ctx->X, (size_t)ctx->pitch4 * 16, (size_t)ctx->d * sizeof(float),
+                    (size_t)ctx->n, cudaMemcpyDeviceToHost));
+    return SVMB200_OK;
+}
+
+} // extern "C"

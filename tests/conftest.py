@@ -1,0 +1,55 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as entry  # noqa: E402
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu")
+
+
+@pytest.fixture(scope="session")
+def pkg():
+    return entry.load_package()
+
+
+@pytest.fixture(scope="session")
+def O():
+    o = entry.load_oracle()
+    o.build()
+    return o
+
+
+@pytest.fixture(scope="session")
+def solver(pkg):
+    """One context on cuda:0 shared by the GPU tests (fails loudly without the built library)."""
+    s = pkg.Solver(0)
+    yield s
+    s.close()
+
+
+_DATA = {}
+
+
+@pytest.fixture(scope="session")
+def dataset(pkg):
+    """dataset(n, split=0) -> (X uint8, digits, y +-1), cached."""
+    def get(n, split=0, seed=587):
+        key = (n, split, seed)
+        if key not in _DATA:
+            X, dg = pkg.datagen.make_dataset(n, seed=seed, split=split)
+            _DATA[key] = (X, dg, pkg.datagen.binary_labels(dg))
+        return _DATA[key]
+    return get
+
+
+def golden(n):
+    import numpy as np
+    path = os.path.join(ROOT, "tests", "golden", f"golden_n{n}.npz")
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not generated")
+    return np.load(path, allow_pickle=False)

@@ -1,0 +1,226 @@
+"""GPU parity tests (pytest -m gpu): the CUDA path, called through the C ABI, against the oracle.
+
+Two levels.  (1) Against ORACLE_ARITH_DEVICE -- the CUDA arithmetic restated on the CPU -- results
+must be BIT-EXACT (kernel rows, pair sequence, alpha, b, f): any race or indexing bug shows up as a
+difference, not as "numerical noise".  (2) Against ORACLE_ARITH_F64 / the golden fixtures from the
+unmodified reference: identical support-vector ID set, identical test accuracy and iteration count
+at the fixture sizes, b within 1e-4 relative, alpha within 1e-4 * C (tolerances per north_star;
+fp32 X vs the reference's FP64 X)."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+B_RTOL = 1e-4
+ALPHA_ATOL_OVER_C = 1e-4
+
+
+def _train_both(solver, O, X, y, chunk=1, **kw):
+    solver.set_train_u8(X, y)
+    out = solver.smo_train(accum_chunk=chunk, trace_cap=100000, **kw)
+    xs, mn, mx = O.scale(X)
+    O.set_device_chunk(chunk)
+    dev = O.smo_train(xs, y, arith=O.ARITH_DEVICE, trace_cap=100000, want_f=True)
+    O.set_device_chunk(1)
+    return out, dev, xs
+
+
+def test_preprocessing_matches_oracle(solver, O, dataset):
+    X, _, y = dataset(700)
+    mn, mx = solver.set_train_u8(X, y)
+    xs, mno, mxo = O.scale(X)
+    assert np.array_equal(mn, mno) and np.array_equal(mx, mxo)
+    assert np.array_equal(solver.get_x_scaled(), xs.astype(np.float32))
+    # FP64 raw input (the reference's CSV path) gives the same rows
+    mn2, mx2 = solver.set_train_f64(X.astype(np.float64), y)
+    assert np.array_equal(mn2, mno) and np.array_equal(mx2, mxo)
+    assert np.array_equal(solver.get_x_scaled(), xs.astype(np.float32))
+    solver.set_train_scaled(xs, y)
+    assert np.array_equal(solver.get_x_scaled(), xs.astype(np.float32))
+
+
+@pytest.mark.parametrize("chunk", [1, 2, 4])
+def test_kernel_row_bit_exact_vs_device_oracle(solver, O, dataset, chunk):
+    X, _, y = dataset(600)
+    X = X.copy()
+    X[17] = X[3]          # duplicate rows -> K = 1 exactly
+    X[40] = 0             # an all-zero row
+    solver.set_train_u8(X, y)
+    xs, _, _ = O.scale(X)
+    x32 = xs.astype(np.float32)
+    O.set_device_chunk(chunk)
+    for i in (0, 3, 40, 599):
+        row = solver.kernel_row(i, 0.00125, chunk)
+        exp = np.array([O.lib().oracle_device_kernel(x32[i], x32[j], 784, 0.00125) for j in range(600)])
+        assert np.array_equal(row, exp), f"row {i} chunk {chunk}"
+        ref = np.array([O.lib().oracle_kernel(xs[i], xs[j], 784, 0.00125) for j in range(600)])
+        assert np.max(np.abs(row - ref) / ref) < (5e-9 if chunk == 1 else 2e-7)
+        assert row[i] == 1.0
+    O.set_device_chunk(1)
+    assert solver.kernel_row(3)[17] == 1.0
+
+
+def test_select_pair_rules(solver, O):
+    rng = np.random.default_rng(5)
+    L = O.lib()
+    for n in (1, 7, 33, 1000, 5000):
+        y = rng.choice([-1, 1], n).astype(np.int32)
+        alpha = rng.choice([0.0, 10.0, 3.5, 1e-13], n)
+        f = rng.choice([-1.0, 1.0, 0.25, np.inf, -np.inf], n)   # massive ties
+        got = solver.select_pair(alpha, f, y)
+        exp = (L.oracle_calc_i_high(alpha, y, f, n, 10.0, 1e-12), L.oracle_calc_i_low(alpha, y, f, n, 10.0, 1e-12))
+        assert got == exp
+    n = 100
+    y = np.ones(n, dtype=np.int32)
+    got = solver.select_pair(np.zeros(n), -y.astype(np.float64), y)
+    assert got == (0, n)          # I_low empty -> n (main3.cpp:129)
+    got = solver.select_pair(np.full(n, 10.0), -y.astype(np.float64), y)
+    assert got == (n, 0)          # I_high empty
+
+
+@pytest.mark.parametrize("n,chunk", [(1, 1), (9, 1), (256, 1), (256, 4), (1000, 2), (2000, 1)])
+def test_training_bit_exact_vs_device_oracle(solver, O, dataset, n, chunk):
+    X, _, y = dataset(max(n, 16))
+    X, y = X[:n], y[:n].copy()
+    if n == 9:
+        y[:] = [1, -1, -1, 1, -1, -1, -1, 1, -1]
+    out, dev, _ = _train_both(solver, O, X, y, chunk)
+    assert out["num_iter"] == dev["num_iter"] and out["stop_reason"] == dev["stop_reason"]
+    assert np.array_equal(solver.get_trace(100000), dev["trace"])
+    assert np.array_equal(out["alpha"], dev["alpha"])
+    assert out["b"] == dev["b"] and out["b_high"] == dev["b_high"] and out["b_low"] == dev["b_low"]
+    assert (out["i_high"], out["i_low"]) == (dev["i_high"], dev["i_low"])
+    assert np.array_equal(solver.get_f(), dev["f"])
+    assert np.array_equal(solver.sv_ids(), O.sv_indices(dev["alpha"]))
+
+
+@pytest.mark.parametrize("n", [256, 2000])
+def test_training_matches_reference_golden(solver, O, dataset, n):
+    g = golden(n)
+    X, dg, y = dataset(n)
+    assert hashlib.sha256(X.tobytes() + dg.tobytes()).hexdigest() == str(g["sha_train"])
+    solver.set_train_u8(X, y)
+    out = solver.smo_train(trace_cap=4096)
+    assert np.array_equal(solver.sv_ids(), g["sv_ids"]), "support-vector ID set differs from the reference"
+    assert abs(out["b"] - float(g["b"])) <= B_RTOL * abs(float(g["b"]))
+    a_ref = np.zeros(n); a_ref[g["sv_ids"]] = g["sv_alpha"]
+    assert np.max(np.abs(out["alpha"] - a_ref)) <= ALPHA_ATOL_OVER_C * 10.0
+    assert out["num_iter"] == int(g["num_iter"])
+    tr = solver.get_trace(4096)
+    assert np.array_equal(tr, g["trace"][:len(tr)]), "pair sequence differs from the reference"
+    m = int(g["m"])
+    Xt, _, yt = dataset(m, split=1)
+    correct, scores = solver.predict_u8(Xt, yt)
+    assert correct == int(g["correct"])
+    assert np.allclose(scores[:256], g["scores_head"][:min(256, m)], rtol=0, atol=1e-4)
+
+
+def test_cache_on_equals_cache_off(solver, O, dataset):
+    X, _, y = dataset(1500)
+    solver.set_train_u8(X, y)
+    off = solver.smo_train(cache_rows=0, trace_cap=100000)
+    tr_off = solver.get_trace(100000)
+    f_off = solver.get_f()
+    for cap in (-1, 64, 2):      # auto, small (FIFO eviction active), degenerate
+        on = solver.smo_train(cache_rows=cap, trace_cap=100000)
+        assert np.array_equal(on["alpha"], off["alpha"]) and on["b"] == off["b"] and on["num_iter"] == off["num_iter"]
+        assert np.array_equal(solver.get_trace(100000), tr_off)
+        assert np.array_equal(solver.get_f(), f_off)
+        assert on["x_passes"] + on["cache_hits"] == on["num_iter"] - 1
+        if cap == -1:
+            assert on["cache_hits"] > 0.5 * on["num_iter"]
+    assert off["cache_hits"] == 0 and off["x_passes"] == off["num_iter"] - 1
+
+
+def test_warm_start_matches_oracle(solver, O, dataset):
+    """init=false: alpha in/out, f rebuilt from alpha (mpi_svm_main2.cpp:167-183)."""
+    n = 800
+    X, _, y = dataset(n)
+    xs, _, _ = O.scale(X)
+    # a feasible non-trivial start: the solution of the first 500 rows, zero elsewhere
+    part = O.smo_train(xs[:500], y[:500])
+    a0 = np.zeros(n); a0[:500] = part["alpha"]
+    dev = O.smo_train(xs, y, alpha0=a0, arith=O.ARITH_DEVICE, trace_cap=100000, want_f=True)
+    solver.set_train_u8(X, y)
+    out = solver.smo_train(alpha0=a0, trace_cap=100000)
+    assert out["num_iter"] == dev["num_iter"]
+    assert np.array_equal(solver.get_trace(100000), dev["trace"])
+    assert np.array_equal(out["alpha"], dev["alpha"]) and out["b"] == dev["b"]
+    ref = O.smo_train(xs, y, alpha0=a0)
+    assert np.array_equal(solver.sv_ids(), O.sv_indices(ref["alpha"]))
+    assert abs(out["b"] - ref["b"]) <= B_RTOL * abs(ref["b"])
+
+
+def test_predict_matches_oracle(solver, O, dataset):
+    n, m = 900, 400
+    X, _, y = dataset(n)
+    Xt, _, yt = dataset(m, split=1)
+    solver.set_train_u8(X, y)
+    out = solver.smo_train()
+    xs, mn, mx = O.scale(X)
+    xt, _, _ = O.scale(Xt, mn, mx)
+    c_dev, s_dev = O.predict(xt, yt, xs, y, out["alpha"], out["b"], arith=O.ARITH_DEVICE)
+    c_gpu, s_gpu = solver.predict_u8(Xt, yt)
+    assert np.array_equal(s_gpu, s_dev) and c_gpu == c_dev            # bit-exact vs the restated arithmetic
+    c_ref, s_ref = O.predict(xt, yt, xs, y, out["alpha"], out["b"])
+    assert c_gpu == c_ref and np.max(np.abs(s_gpu - s_ref)) < 1e-5     # vs the reference's FP64 loop
+    c_ge, _ = solver.predict_u8(Xt, yt, ge_zero=True)                   # MPI programs' ">= 0" rule
+    assert c_ge == O.predict(xt, yt, xs, y, out["alpha"], out["b"], ge_zero=True, arith=O.ARITH_DEVICE)[0]
+    c_f64, s_f64 = solver.predict_f64(Xt.astype(np.float64), yt)
+    assert c_f64 == c_gpu and np.array_equal(s_f64, s_gpu)
+
+
+@pytest.mark.parametrize("d", [1, 4, 30, 100, 257, 1024])
+def test_other_feature_counts(solver, O, d):
+    rng = np.random.default_rng(d)
+    n = 300
+    X = rng.uniform(-3, 5, (n, d))
+    w = rng.normal(size=d)
+    y = np.where(X @ w + rng.normal(0, 0.5, n) > np.median(X @ w), 1, -1).astype(np.int32)
+    solver.set_train_f64(X, y)
+    gamma = 0.5 / d
+    out = solver.smo_train(gamma=gamma, C=1.0, trace_cap=100000)
+    xs, _, _ = O.scale(X)
+    p = O.default_params(gamma=gamma, C=1.0)
+    dev = O.smo_train(xs, y, params=p, arith=O.ARITH_DEVICE, trace_cap=100000)
+    assert out["num_iter"] == dev["num_iter"]
+    assert np.array_equal(out["alpha"], dev["alpha"]) and out["b"] == dev["b"]
+    ref = O.smo_train(xs, y, params=p)
+    assert np.array_equal(solver.sv_ids(), O.sv_indices(ref["alpha"]))
+
+
+def test_abnormal_stops_are_stats_not_errors(solver, O, dataset, pkg):
+    X, _, y = dataset(300)
+    solver.set_train_u8(X, y)
+    out = solver.smo_train(max_iter=10)
+    xs, _, _ = O.scale(X)
+    dev = O.smo_train(xs, y, params=O.default_params(max_iter=10), arith=O.ARITH_DEVICE)
+    assert out["stop_reason"] == 4 == dev["stop_reason"] and out["num_iter"] == 11 == dev["num_iter"]
+    assert np.array_equal(out["alpha"], dev["alpha"]) and out["b"] == dev["b"]
+    yp = np.ones(300, dtype=np.int32)                        # one class only: I_low is empty at alpha = 0
+    solver.set_train_u8(X, yp)
+    out = solver.smo_train()
+    assert out["stop_reason"] == 1 and out["num_iter"] == 1 and out["i_low"] == 300 and out["i_high"] == 0
+    X2 = X.copy(); X2[1] = X2[0]                             # duplicate rows with opposite labels: eta = 0
+    y2 = y.copy(); y2[:] = -1; y2[0] = 1; X2[2:] = X2[0]
+    solver.set_train_u8(X2, y2)
+    out = solver.smo_train()
+    assert out["stop_reason"] == 3
+
+
+def test_errors_are_reported(pkg):
+    s = pkg.Solver(0)
+    with pytest.raises(pkg.SvmB200Error, match="before"):
+        s.smo_train()
+    with pytest.raises(pkg.SvmB200Error):
+        s.set_train_f64(np.zeros((4, 2000)), np.ones(4, dtype=np.int32))   # d > 1024
+    X = np.zeros((8, 4)); y = np.array([1, -1] * 4, dtype=np.int32)
+    s.set_train_f64(X, y)
+    s.n = 8
+    with pytest.raises(pkg.SvmB200Error, match="wss"):
+        s.smo_train(wss=2)
+    s.close()
