@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py -- the headline benchmark of the RBF-SMO hot path (BASELINE.json: SMO iters/sec and train
+seconds at 60k x 784, as a fraction of the HBM roofline).
+
+A "step" is one SMO iteration: one pass of the hot path over the whole training matrix (both kernel
+rows from one read of X, f update, working-pair selection, the record exchange).  The timed region is
+exactly K iterations of the persistent kernel (svmb200_params.max_iter = K), X already resident in
+HBM, timed with CUDA events on the launching stream inside the C ABI (svmb200_stats.smo_ms), row
+cache OFF so that every iteration streams X (N*784*4 algorithmic bytes).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n ROWS]
+
+One JSON line on stdout (rank 0).  Extra keys beyond the contract: `train` (full training to
+convergence, cache off / on, with the SV-set check against the 60k golden fixture) and `cached`.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as entry  # noqa: E402
+
+N_ROWS = 60000
+D = 784
+SEED = 587
+METRIC = "smo_iters_per_sec"
+UNIT = "iter/s"
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device = device
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.device), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1])); mx.append(float(p[2])); power.append(float(p[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def load_workload(pkg, n, rank=0):
+    """Synthetic MNIST-shaped rows; rank r's binary problem is 'digit (1 + r) % 10 vs rest' on the same X."""
+    X, digits = pkg.datagen.make_dataset(n, seed=SEED)
+    y = pkg.datagen.binary_labels(digits, positive_digit=(1 + rank) % 10)
+    return X, digits, y
+
+
+def golden_sv(n):
+    path = os.path.join(ROOT, "tests", "golden", f"golden_n{n}.npz")
+    if os.path.exists(path):
+        g = np.load(path)
+        return g["sv_ids"], float(g["b"]), int(g["num_iter"])
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """--impl reference: the reference's own CPU code for the path (oracle/_ref: code/main3.cpp's
+    calc_i_high / calc_i_low / kernel / calculate_U_V, compiled unmodified) on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import ctypes as C
+    O = entry.load_oracle()
+    pkg = entry.load_package()
+    n = args.n
+    X, digits, y = load_workload(pkg, n)
+    xs, _, _ = O.scale(X)
+    R = O.ref()
+    kind = "reference" if R is not None else "port"
+    budget_s = float(os.environ.get("SVMB200_REF_BUDGET_S", "60"))
+
+    def run_iters(k):
+        t = time.perf_counter()
+        if R is not None:
+            rows = C.c_int64()
+            done = R.ref_smo_iterations(xs, y, n, D, 10.0, k, None, C.byref(rows))
+        else:
+            p = O.default_params(max_iter=k)
+            done = O.smo_train(xs, y, params=p)["num_iter"] - 1
+        return done, time.perf_counter() - t
+
+    done, t = run_iters(max(1, min(args.warmup, 3)))          # warm-up doubles as the cost probe
+    per_iter = t / max(done, 1)
+    k = int(max(1, min(args.steps, budget_s / per_iter)))
+    done, t = run_iters(k)
+    value = done / t
+    sample = (f"first {done} of {args.steps} SMO iterations from alpha=0 on the full {n}x{D} workload (FP64), "
+              f"driven through the reference's own functions by oracle/ref_wrapper.cpp:ref_smo_iterations; "
+              f"the serial reference uses 1 thread")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t / done, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{n}x{D} RBF SMO, binary one-vs-rest (digit 1), C=10 gamma=0.00125, seed {SEED}"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU path in the product")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg = entry.load_package()
+    n = args.n
+    X, digits, y = load_workload(pkg, n, rank)
+    solver = pkg.Solver(local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # X resident in HBM before the timed region
+    solver.set_train_u8(X, y)
+    for _ in range(max(args.warmup, 3)):                         # warm-up launches (not timed)
+        solver.smo_train(max_iter=50, cache_rows=0)
+
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    out = solver.smo_train(max_iter=args.steps, cache_rows=0)
+    barrier()
+    wall = time.perf_counter() - t0
+    steps_done = out["num_iter"] - 1
+    # a second, longer stretch keeps the sampler busy long enough to see clocks under load
+    reps = []
+    for _ in range(3):
+        r = solver.smo_train(max_iter=args.steps, cache_rows=0)
+        reps.append(r["smo_ms"])
+    clocks = sampler.stop()
+    smo_ms = float(np.median([out["smo_ms"]] + reps))
+    if world > 1:
+        t = torch.tensor([smo_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        smo_ms = float(t.item())
+        s = torch.tensor([steps_done], device="cuda", dtype=torch.float64)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+        total_steps = float(s.item())
+    else:
+        total_steps = float(steps_done)
+    value = total_steps / (smo_ms / 1e3)
+    ms_per_step = smo_ms / max(steps_done, 1)
+
+    # ---- e2e: the whole job through the C ABI from HOST buffers: upload + min/max + scale + SMO to
+    # convergence + alpha back (the reference's "training time" bracket, gpu_svm_main3.cu:525->612)
+    e2e_runs = {}
+    for label, cache in (("cache_off", 0), ("cache_on", -1)):
+        barrier()
+        t0 = time.perf_counter()
+        solver.set_train_u8(X, y)
+        full = solver.smo_train(cache_rows=cache)
+        barrier()
+        secs = time.perf_counter() - t0
+        e2e_runs[label] = {"train_secs": secs, "smo_secs": full["smo_ms"] / 1e3, "iterations": full["num_iter"] - 1,
+                           "iters_per_sec": (full["num_iter"] - 1) / secs, "n_sv": full["n_sv"], "b": full["b"],
+                           "stop_reason": pkg.STOP_NAMES[full["stop_reason"]], "x_passes": full["x_passes"],
+                           "cache_hits": full["cache_hits"]}
+        if rank == 0:
+            g = golden_sv(n)
+            if g is not None:
+                sv = solver.sv_ids()
+                e2e_runs[label]["sv_set_equals_reference"] = bool(np.array_equal(sv, g[0]))
+                e2e_runs[label]["b_rel_err"] = abs(full["b"] - g[1]) / max(1.0, abs(g[1]))
+                e2e_runs[label]["reference_iterations"] = g[2] - 1
+    e2e_val = e2e_runs["cache_off"]["iters_per_sec"]
+    e2e_iters = max(e2e_runs["cache_off"]["iterations"], 1)
+    if world > 1:
+        t = torch.tensor([e2e_runs["cache_off"]["train_secs"], float(e2e_runs["cache_off"]["iterations"])],
+                         device="cuda", dtype=torch.float64)
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        e2e_val = float(tsum[1].item() / tmax[0].item())
+
+    peak, peak_src = measured_peak()
+    row_bytes = ((D + 3) // 4) * 16
+    alg_bytes = n * row_bytes                                     # X once per iteration
+    achieved = alg_bytes / (ms_per_step * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "kernel": "smo_persistent_kernel<7,1>",
+                "algorithmic_bytes_per_iteration": alg_bytes,
+                "note": "one launch runs all K iterations; achieved = K * N*784*4 / kernel time (CUDA events)"}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("dram_bytes_per_iteration")
+        except Exception:
+            pass
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import ctypes as C
+        O = entry.load_oracle()
+        xs, _, _ = O.scale(X)
+        R = O.ref()
+        k = args.cpu_iters
+        t0 = time.perf_counter()
+        if R is not None:
+            rows = C.c_int64()
+            done = R.ref_smo_iterations(xs, y, n, D, 10.0, k, None, C.byref(rows))
+            kind = "reference"
+        else:
+            done = O.smo_train(xs, y, params=O.default_params(max_iter=k))["num_iter"] - 1
+            kind = "port"
+        secs = time.perf_counter() - t0
+        cpu_baseline = {"value": done / secs, "unit": UNIT, "cores": 1, "kind": kind,
+                        "sample": f"first {done} SMO iterations from alpha=0 on the full {n}x{D} workload (FP64, serial "
+                                  f"reference functions of code/main3.cpp via oracle/ref_wrapper.cpp); {secs:.1f} s",
+                        "host_cores_available": os.cpu_count()}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 X / f64 state", "data": "synthetic",
+                "config": {"workload": f"{n}x{D} RBF SMO, binary one-vs-rest (digit 1 + rank), C=10 gamma=0.00125, seed {SEED}",
+                           "l2": f"X = {alg_bytes / 1e6:.0f} MB per iteration vs 126 MB L2: inputs larger than L2" if alg_bytes > 126e6
+                           else "X fits in L2 (L2-resident regime, not an HBM number)",
+                           "row_cache": "off in the timed region", "steps_done": steps_done,
+                           "parallelism": "1 GPU" if world == 1 else f"{world} independent one-vs-rest problems (one digit per GPU)"},
+                "roofline": roofline, "cpu_baseline": cpu_baseline,
+                "e2e": {"value": e2e_val, "unit": UNIT,
+                        "h2d_bytes_per_step": (X.nbytes + y.nbytes) / e2e_iters, "d2h_bytes_per_step": (8 * n) / e2e_iters,
+                        "h2d_bytes_per_job": X.nbytes + y.nbytes, "d2h_bytes_per_job": 8 * n,
+                        "what": "whole job from host buffers through the C ABI: svmb200_set_train_u8 (H2D + min/max + scale) + "
+                                "svmb200_smo_train to convergence (row cache off) + alpha D2H; value = iterations / wall seconds"},
+                "gpu_launches": out["launches"], "clocks": clocks, "wall_s_timed_call": wall,
+                "train": e2e_runs}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--n", type=int, default=N_ROWS)
+    ap.add_argument("--cpu-iters", type=int, default=150)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -254,15 +254,17 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
     // the ring: rows of this warp's range are requested in order, cyclically, for ever
     unsigned issued = 0, consumed = 0;   // row copies requested / used so far (mod 2^32 is fine)
     int pf_row = 0;                      // next row of the range to request
-    auto issue_one = [&]() {             // lane 0 only
-        const int s = issued % KS;
-        mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
-        bulk_g2s(my_slots + (size_t)s * row_bytes, a.X + (size_t)(w0 + pf_row) * a.pitch4 * 4, (unsigned)row_bytes,
-                 &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
+    auto issue_one = [&]() {             // called by the whole warp (counters stay warp-uniform); lane 0 issues
+        if (lane == 0) {
+            const int s = issued % KS;
+            mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
+            bulk_g2s(my_slots + (size_t)s * row_bytes, a.X + (size_t)(w0 + pf_row) * a.pitch4 * 4, (unsigned)row_bytes,
+                     &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
+        }
         ++issued;
         if (++pf_row == m) pf_row = 0;
     };
-    if (lane == 0 && m > 0)
+    if (m > 0)
         for (int s = 0; s < KS; ++s) issue_one();
 
     // ---- exchange 0: selection over the initial state (main3.cpp:203-204 in the first iteration)
@@ -385,7 +387,8 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
                     if (lane == t) { my_dh = dh; my_dl = dl; }
                     // the slot is free again: request the next row of the ring into it
                     __syncwarp();
-                    if (lane == 0) { fence_proxy_async(); issue_one(); }
+                    fence_proxy_async();
+                    issue_one();
                 }
                 if (lane < cnt) {
                     const double kh = svm_exp(-a.gamma * my_dh);
