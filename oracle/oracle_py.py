@@ -13,6 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ARITH_F64, ARITH_DEVICE = 0, 1
+DEFAULT_CHUNK = 4   # the library's default svmb200_params.accum_chunk
 STOP_NAMES = {0: "converged", 1: "not_found", 2: "infeasible_uv", 3: "nonpositive_eta", 4: "max_iter"}
 
 
@@ -74,6 +75,8 @@ def lib():
                                      C.c_size_t, C.c_double, C.c_double, C.c_int, C.c_int, C.c_void_p]
         L.oracle_device_exp.restype = C.c_double
         L.oracle_device_exp.argtypes = [C.c_double]
+        L.oracle_device_dot.restype = C.c_double
+        L.oracle_device_dot.argtypes = [_f32(), _f32(), C.c_size_t]
         L.oracle_device_sqdist.restype = C.c_double
         L.oracle_device_sqdist.argtypes = [_f32(), _f32(), C.c_size_t]
         L.oracle_set_device_chunk.argtypes = [C.c_int]

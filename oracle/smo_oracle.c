@@ -142,41 +142,41 @@ double oracle_device_exp(double x)
     return (p * s1.f) * s2.f;
 }
 
-static int g_device_chunk = 1; /* fp32 squares summed before widening to FP64: 1, 2 or 4 */
-void oracle_set_device_chunk(int ch) { g_device_chunk = (ch == 2 || ch == 4) ? ch : 1; }
+static int g_device_chunk = 4; /* fp32 squares summed before widening to FP64: 1, 2 or 4 */
+void oracle_set_device_chunk(int ch) { g_device_chunk = (ch == 1 || ch == 2) ? ch : 4; }
 int oracle_get_device_chunk(void) { return g_device_chunk; }
 
-double oracle_device_sqdist(const float *a, const float *b, size_t d)
+/* dot product of two fp32 rows as the CUDA path forms it: lane l = q mod 32 owns the float4 groups
+ * q = l, l+32, ...; the products of `chunk` consecutive elements are summed in fp32 (fmaf), widened
+ * and added to the lane's FP64 sum; the 32 lane sums are combined by an xor-butterfly 16,8,4,2,1. */
+double oracle_device_dot(const float *a, const float *b, size_t d)
 {
     double lane[32];
     for (int l = 0; l < 32; ++l) lane[l] = 0.0;
     size_t d4 = (d + 3) / 4;
     for (size_t q = 0; q < d4; ++q) {
-        float df[4];
+        float av[4], bv[4];
         for (int c = 0; c < 4; ++c) {
             size_t k = 4 * q + c;
-            float av = k < d ? a[k] : 0.0f, bv = k < d ? b[k] : 0.0f; /* rows are zero-padded */
-            df[c] = av - bv;
+            av[c] = k < d ? a[k] : 0.0f; /* rows are zero-padded */
+            bv[c] = k < d ? b[k] : 0.0f;
         }
         double acc = lane[q & 31];
         if (g_device_chunk == 4) {
-            float p = df[0] * df[0];
-            p = fmaf(df[1], df[1], p);
-            p = fmaf(df[2], df[2], p);
-            p = fmaf(df[3], df[3], p);
+            float p = av[0] * bv[0];
+            p = fmaf(av[1], bv[1], p);
+            p = fmaf(av[2], bv[2], p);
+            p = fmaf(av[3], bv[3], p);
             acc = acc + (double)p;
         } else if (g_device_chunk == 2) {
-            float p = df[0] * df[0];
-            p = fmaf(df[1], df[1], p);
+            float p = av[0] * bv[0];
+            p = fmaf(av[1], bv[1], p);
             acc = acc + (double)p;
-            float t = df[2] * df[2];
-            t = fmaf(df[3], df[3], t);
+            float t = av[2] * bv[2];
+            t = fmaf(av[3], bv[3], t);
             acc = acc + (double)t;
         } else {
-            for (int c = 0; c < 4; ++c) {
-                double e = (double)df[c];
-                acc = fma(e, e, acc);
-            }
+            for (int c = 0; c < 4; ++c) acc = fma((double)av[c], (double)bv[c], acc);
         }
         lane[q & 31] = acc;
     }
@@ -188,13 +188,30 @@ double oracle_device_sqdist(const float *a, const float *b, size_t d)
     return lane[0];
 }
 
+/* squared distance from the squared norms: (|a|^2 + |b|^2) - 2 a.b, clamped at 0 */
+double oracle_device_sqdist_n(double na, double nb, double ab)
+{
+    double s = (na + nb) - 2.0 * ab;
+    return s < 0.0 ? 0.0 : s;
+}
+
+double oracle_device_sqdist(const float *a, const float *b, size_t d)
+{
+    return oracle_device_sqdist_n(oracle_device_dot(a, a, d), oracle_device_dot(b, b, d), oracle_device_dot(a, b, d));
+}
+
 double oracle_device_kernel(const float *a, const float *b, size_t d, double gamma)
 {
     return oracle_device_exp(-gamma * oracle_device_sqdist(a, b, d));
 }
 
+static double device_kernel_n(const float *a, const float *b, double na, double nb, size_t d, double gamma)
+{
+    return oracle_device_exp(-gamma * oracle_device_sqdist_n(na, nb, oracle_device_dot(a, b, d)));
+}
+
 /* one kernel row K(i, .) in the chosen arithmetic */
-static void kernel_row(const double *x, const float *x32, size_t n, size_t d, size_t i,
+static void kernel_row(const double *x, const float *x32, const double *sqn, size_t n, size_t d, size_t i,
                        double gamma, int arith, double *row)
 {
     if (arith == ORACLE_ARITH_F64) {
@@ -202,7 +219,7 @@ static void kernel_row(const double *x, const float *x32, size_t n, size_t d, si
             row[j] = oracle_kernel(x + i * d, x + j * d, d, gamma);
     } else {
         for (size_t j = 0; j < n; ++j)
-            row[j] = oracle_device_kernel(x32 + i * d, x32 + j * d, d, gamma);
+            row[j] = device_kernel_n(x32 + i * d, x32 + j * d, sqn[i], sqn[j], d, gamma);
     }
 }
 
@@ -217,9 +234,12 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
     double *K_h = (double *)calloc(n ? n : 1, sizeof(double));
     double *K_l = (double *)calloc(n ? n : 1, sizeof(double));
     float *x32 = NULL;
+    double *sqn = NULL;
     if (arith == ORACLE_ARITH_DEVICE) {
         x32 = (float *)malloc(sizeof(float) * (n * d ? n * d : 1));
+        sqn = (double *)malloc(sizeof(double) * (n ? n : 1));
         for (size_t k = 0; k < n * d; ++k) x32[k] = (float)x[k];
+        for (size_t i = 0; i < n; ++i) sqn[i] = oracle_device_dot(x32 + i * d, x32 + i * d, d);
     }
 
     if (init) {
@@ -235,7 +255,7 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
                 if (alpha[j] == 0.0) continue;
                 double kij = (arith == ORACLE_ARITH_F64)
                                  ? oracle_kernel(x + j * d, x + i * d, d, gamma)
-                                 : oracle_device_kernel(x32 + j * d, x32 + i * d, d, gamma);
+                                 : device_kernel_n(x32 + j * d, x32 + i * d, sqn[j], sqn[i], d, gamma);
                 sum += alpha[j] * y[j] * kij;
             }
             f[i] = sum - (double)y[i];
@@ -260,12 +280,12 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
 
         if (i_high != i_high_prev) { /* :216-223 */
             i_high_prev = i_high;
-            kernel_row(x, x32, n, d, i_high, gamma, arith, K_h);
+            kernel_row(x, x32, sqn, n, d, i_high, gamma, arith, K_h);
             ++rows;
         }
         if (i_low != i_low_prev) { /* :225-232 */
             i_low_prev = i_low;
-            kernel_row(x, x32, n, d, i_low, gamma, arith, K_l);
+            kernel_row(x, x32, sqn, n, d, i_low, gamma, arith, K_l);
             ++rows;
         }
         if (trace && ntrace < trace_cap) {
@@ -311,7 +331,7 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
         res->rows_computed = rows;
     }
     if (f_out) memcpy(f_out, f, sizeof(double) * n);
-    free(f); free(K_h); free(K_l); free(x32);
+    free(f); free(K_h); free(K_l); free(x32); free(sqn);
     return 0;
 }
 

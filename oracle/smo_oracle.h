@@ -46,8 +46,8 @@ enum {
 enum {
     ORACLE_ARITH_F64      = 0, /* the reference's arithmetic: sequential FP64 sum, libm exp */
     ORACLE_ARITH_DEVICE   = 1  /* the CUDA path's arithmetic restated op for op (fp32 X,
-                                  float4-chunk fp32 partial sums, FP64 lane sums, fixed
-                                  butterfly order, svm_exp): used to check the GPU bit for bit */
+                                  squared norms + fp32-chunk dot products, FP64 lane sums,
+                                  fixed butterfly order, svm_exp): used to check the GPU bit for bit */
 };
 
 typedef struct {
@@ -94,11 +94,15 @@ int    oracle_predict(const double *x_test, const int *y_test, size_t m,
 /* ---- the CUDA path's arithmetic, restated (ORACLE_ARITH_DEVICE) ---- */
 /* exp() restated with IEEE +,*,fma only, so host and device agree bit for bit */
 double oracle_device_exp(double x);
-/* fp32 squares summed before widening to FP64 (svmb200_params.accum_chunk): 1 (default), 2 or 4 */
+/* fp32 squares summed before widening to FP64 (svmb200_params.accum_chunk): 1, 2 or 4 (default, as the library) */
 void   oracle_set_device_chunk(int ch);
 int    oracle_get_device_chunk(void);
-/* squared distance of two fp32 rows: fp32 differences, fp32 fma over each float4, FP64 lane
- * sums over lanes l = q mod 32, xor-butterfly 16,8,4,2,1 */
+/* dot product of two fp32 rows: products of `chunk` consecutive elements summed in fp32 (fmaf),
+ * widened and added to the FP64 sum of lane l = q mod 32 (q = float4 group), lane sums combined by
+ * an xor-butterfly 16,8,4,2,1 */
+double oracle_device_dot(const float *a, const float *b, size_t d);
+/* squared distance max(0, (|a|^2 + |b|^2) - 2 a.b) from those dot products */
+double oracle_device_sqdist_n(double na, double nb, double ab);
 double oracle_device_sqdist(const float *a, const float *b, size_t d);
 double oracle_device_kernel(const float *a, const float *b, size_t d, double gamma);
 

@@ -73,6 +73,25 @@ __global__ void scale_to_f32_kernel(const T *__restrict__ X, long long n, int d,
     }
 }
 
+// ---- squared norms |x_j|^2: the dot product of every row with itself, formed exactly as the solver
+// forms x_i . x_j (a warp per row), so that duplicates are at distance exactly 0
+template <int Q, int CH>
+__global__ void row_sqnorm_kernel(const float *__restrict__ X, long long n, int pitch4, double *__restrict__ sqn)
+{
+    const int lane = threadIdx.x & 31;
+    const long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (j >= n) return;
+    const float4 *xj = reinterpret_cast<const float4 *>(X) + (size_t)j * pitch4;
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < Q; ++i) {
+        const int q = i * 32 + lane;
+        if (q < pitch4) { const float4 v = __ldg(xj + q); accum_dot<CH>(v, v, acc); }
+    }
+    acc = warp_sum_butterfly(acc);
+    if (lane == 0) sqn[j] = acc;
+}
+
 // ---- solver state init: alpha = 0, f = -y (code/main3.cpp:167-172; gpu_svm_main3.cu:152-161)
 __global__ void init_state_kernel(const int *__restrict__ y, long long n, double *__restrict__ f, double *__restrict__ alpha,
                                   long long *__restrict__ cacheq, int zero_alpha, int set_f)
@@ -84,10 +103,11 @@ __global__ void init_state_kernel(const int *__restrict__ y, long long n, double
     }
 }
 
-// ---- gather rows (support vectors) into a dense block
-__global__ void gather_rows_kernel(const float *__restrict__ X, int pitch4, const int *__restrict__ ids, int count,
-                                   float *__restrict__ out)
+// ---- gather rows (support vectors) and their squared norms into a dense block
+__global__ void gather_rows_kernel(const float *__restrict__ X, const double *__restrict__ sqn, int pitch4,
+                                   const int *__restrict__ ids, int count, float *__restrict__ out, double *__restrict__ out_n)
 {
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) out_n[k] = sqn[ids[k]];
     const long long total = (long long)count * pitch4;
     for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
         const long long k = g / pitch4;
@@ -109,8 +129,8 @@ constexpr int DEC_TILE = 16;
 
 template <int Q, int CH>
 __global__ void __launch_bounds__(DEC_THREADS, 1)
-decision_kernel(const float *__restrict__ Xq, long long m, const float *__restrict__ SV, const double *__restrict__ coef,
-                int nsv, int pitch4, double gamma, double init, const int *__restrict__ ysub, double *__restrict__ out)
+decision_kernel(const float *__restrict__ Xq, long long m, const float *__restrict__ SV, const double *__restrict__ svn,
+                const double *__restrict__ coef, int nsv, int pitch4, double gamma, double init, const int *__restrict__ ysub, double *__restrict__ out)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -134,6 +154,11 @@ decision_kernel(const float *__restrict__ Xq, long long m, const float *__restri
         qv[i] = (active && q < pitch4) ? __ldg(reinterpret_cast<const float4 *>(Xq) + (size_t)qi * pitch4 + q)
                                        : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    double qn = 0.0;                                                   // |q|^2, the same way the solver forms norms
+#pragma unroll
+    for (int i = 0; i < Q; ++i)
+        if (i * 32 + lane < pitch4) accum_dot<CH>(qv[i], qv[i], qn);
+    qn = warp_sum_butterfly(qn);
 
     const int ntiles = (nsv + DEC_TILE - 1) / DEC_TILE;
     auto issue_tile = [&](int t) {      // thread 0
@@ -157,12 +182,13 @@ decision_kernel(const float *__restrict__ Xq, long long m, const float *__restri
 #pragma unroll
             for (int i = 0; i < Q; ++i) {
                 const int q = i * 32 + lane;
-                if (q < pitch4) accum_sq<CH>(row[q], qv[i], acc);
+                if (q < pitch4) accum_dot<CH>(row[q], qv[i], acc);
             }
             acc = warp_sum_butterfly(acc);
             if (lane == r) myk = acc;
         }
-        myk = svm_exp(-gamma * myk);                                  // lanes >= rows compute a value nobody reads
+        const double myn = lane < rows ? svn[t * DEC_TILE + lane] : 0.0;
+        myk = svm_exp(-gamma * sqdist_from_dot(qn, myn, myk));        // lanes >= rows compute a value nobody reads
         const double mycoef = lane < rows ? coef[t * DEC_TILE + lane] : 0.0;
         for (int r = 0; r < rows; ++r) {
             const double k = __shfl_sync(FULL, myk, r);
@@ -197,8 +223,8 @@ __global__ void count_correct_kernel(const double *__restrict__ scores, const in
 
 // ---- introspection: one kernel row exactly as the solver forms it (a warp per row, no staging)
 template <int Q, int CH>
-__global__ void kernel_row_kernel(const float *__restrict__ X, long long n, int pitch4, long long pivot, double gamma,
-                                  double *__restrict__ out)
+__global__ void kernel_row_kernel(const float *__restrict__ X, const double *__restrict__ sqn, long long n, int pitch4,
+                                  long long pivot, double gamma, double *__restrict__ out)
 {
     const int lane = threadIdx.x & 31;
     const long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -209,35 +235,31 @@ __global__ void kernel_row_kernel(const float *__restrict__ X, long long n, int 
 #pragma unroll
     for (int i = 0; i < Q; ++i) {
         const int q = i * 32 + lane;
-        if (q < pitch4) accum_sq<CH>(__ldg(xj + q), __ldg(xp + q), acc);
+        if (q < pitch4) accum_dot<CH>(__ldg(xj + q), __ldg(xp + q), acc);
     }
     acc = warp_sum_butterfly(acc);
-    if (lane == 0) out[j] = svm_exp(-gamma * acc);
+    if (lane == 0) out[j] = svm_exp(-gamma * sqdist_from_dot(sqn[pivot], sqn[j], acc));
 }
 
 // ---- introspection: one working-set selection with the solver's own compare (single CTA)
 __global__ void select_pair_kernel(const double *__restrict__ alpha, const double *__restrict__ f, const int *__restrict__ y,
                                    long long n, double C, double eps, long long *__restrict__ out)
 {
-    __shared__ double sfmin[32], sfmax[32];
-    __shared__ int simin[32], simax[32];
+    __shared__ Best slo[32], shi[32];
     LocalBest b;
     best_init(b);
-    for (long long j = threadIdx.x; j < n; j += blockDim.x) {
-        if (in_I_high(y[j], alpha[j], C, eps) && f[j] < b.fmin) { b.fmin = f[j]; b.imin = (int)j; }
-        if (in_I_low(y[j], alpha[j], C, eps) && f[j] > b.fmax) { b.fmax = f[j]; b.imax = (int)j; }
-    }
+    for (long long j = threadIdx.x; j < n; j += blockDim.x) best_consider(b, j, f[j], alpha[j], y[j], -1, C, eps);
     best_warp_reduce(b);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) { sfmin[warp] = b.fmin; simin[warp] = b.imin; sfmax[warp] = b.fmax; simax[warp] = b.imax; }
+    if (lane == 0) { slo[warp] = b.lo; shi[warp] = b.hi; }
     __syncthreads();
     if (warp == 0) {
         best_init(b);
-        if (lane < (int)(blockDim.x >> 5)) { b.fmin = sfmin[lane]; b.imin = simin[lane]; b.fmax = sfmax[lane]; b.imax = simax[lane]; }
+        if (lane < (int)(blockDim.x >> 5)) { b.lo = slo[lane]; b.hi = shi[lane]; }
         best_warp_reduce(b);
         if (lane == 0) {
-            out[0] = b.imin == IDX_NONE ? n : b.imin;
-            out[1] = b.imax == IDX_NONE ? n : b.imax;
+            out[0] = b.lo.idx == IDX_NONE ? n : b.lo.idx;
+            out[1] = b.hi.idx == IDX_NONE ? n : b.hi.idx;
         }
     }
 }

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -16,6 +17,19 @@
 using namespace svm;
 
 static thread_local std::string g_create_error;
+#ifdef SVM_TIMING
+static long long *g_timing_dev = nullptr;
+extern "C" int svmb200_debug_timing(long long *out, int rows)
+{
+    if (!g_timing_dev) return -1;
+    return cudaMemcpy(out, g_timing_dev, (size_t)rows * 8 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
+}
+extern "C" int svmb200_debug_timing_grid(long long *out)
+{
+    if (!g_timing_dev) return -1;
+    return cudaMemcpy(out, g_timing_dev + 4096 * 8, (size_t)8 * 160 * 4 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
+}
+#endif
 
 struct svmb200_ctx {
     int device = 0;
@@ -30,6 +44,8 @@ struct svmb200_ctx {
     int d = 0, pitch4 = 0;
     float *X = nullptr;
     int *y = nullptr;
+    double *sqn = nullptr;      // |x_j|^2 formed with accumulation chunk sqn_chunk (0 = not computed)
+    int sqn_chunk = 0;
     double *minv = nullptr, *maxv = nullptr;
     bool have_stats = false, have_train = false;
 
@@ -52,6 +68,7 @@ struct svmb200_ctx {
     std::vector<int> sv_ids;
     float *svX = nullptr;
     double *svcoef = nullptr;
+    double *svn = nullptr;
     int sv_alloc = 0;
 
     // generic scratch
@@ -165,7 +182,7 @@ void svmb200_destroy(svmb200_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    cudaFree(ctx->X); cudaFree(ctx->y); cudaFree(ctx->minv); cudaFree(ctx->maxv);
+    cudaFree(ctx->X); cudaFree(ctx->y); cudaFree(ctx->sqn); cudaFree(ctx->svn); cudaFree(ctx->minv); cudaFree(ctx->maxv);
     cudaFree(ctx->f); cudaFree(ctx->alpha); cudaFree(ctx->cacheq); cudaFree(ctx->cacheK);
     cudaFree(ctx->rec); cudaFree(ctx->result); cudaFree(ctx->trace);
     cudaFree(ctx->svX); cudaFree(ctx->svcoef); cudaFree(ctx->scratch);
@@ -185,11 +202,12 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
     if (pitch4 > 256) FAIL(SVMB200_ELIMIT, "d=%d exceeds the 1024-feature limit of the in-register pivot rows", d);
     CK(cudaSetDevice(ctx->device));
     if (n != ctx->n || d != ctx->d) {
-        if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
+        if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->sqn) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
             dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv))
             return SVMB200_ECUDA;
         CK(cudaMalloc(&ctx->X, (size_t)n * pitch4 * 16));
         CK(cudaMalloc(&ctx->y, (size_t)n * sizeof(int)));
+        CK(cudaMalloc(&ctx->sqn, (size_t)n * sizeof(double)));
         CK(cudaMalloc(&ctx->f, (size_t)n * sizeof(double)));
         CK(cudaMalloc(&ctx->alpha, (size_t)n * sizeof(double)));
         CK(cudaMalloc(&ctx->cacheq, (size_t)n * sizeof(long long)));
@@ -202,6 +220,7 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
     ctx->have_train = false;
     ctx->trained = false;
     ctx->have_stats = false;
+    ctx->sqn_chunk = 0;
     return 0;
 }
 
@@ -281,92 +300,133 @@ static int q_for_pitch(int pitch4)
     return 8;
 }
 
-template <int Q, int CH>
+template <int Q, int CH, int THREADS>
 static cudaError_t launch_smo(const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
 {
-    cudaError_t e = cudaFuncSetAttribute(smo_persistent_kernel<Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(smo_persistent_kernel<Q, CH, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     void *kargs[] = {(void *)&args};
-    return cudaLaunchCooperativeKernel((void *)smo_persistent_kernel<Q, CH>, dim3(grid), dim3(SMO_THREADS), kargs, smem, stream);
+    return cudaLaunchCooperativeKernel((void *)smo_persistent_kernel<Q, CH, THREADS>, dim3(grid), dim3(THREADS), kargs, smem, stream);
 }
 
+// CTA sizes other than 512 threads exist for the MNIST-shaped rows only (Q = 7)
 template <int CH>
-static cudaError_t launch_smo_q(int Q, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+static cudaError_t launch_smo_q(int Q, int threads, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
 {
     switch (Q) {
-    case 1: return launch_smo<1, CH>(args, grid, smem, stream);
-    case 2: return launch_smo<2, CH>(args, grid, smem, stream);
-    case 4: return launch_smo<4, CH>(args, grid, smem, stream);
-    case 7: return launch_smo<7, CH>(args, grid, smem, stream);
-    default: return launch_smo<8, CH>(args, grid, smem, stream);
+    case 1: return launch_smo<1, CH, 512>(args, grid, smem, stream);
+    case 2: return launch_smo<2, CH, 512>(args, grid, smem, stream);
+    case 4: return launch_smo<4, CH, 512>(args, grid, smem, stream);
+    case 7:
+        if (threads == 256) return launch_smo<7, CH, 256>(args, grid, smem, stream);
+        if (threads == 384) return launch_smo<7, CH, 384>(args, grid, smem, stream);
+        return launch_smo<7, CH, 512>(args, grid, smem, stream);
+    default: return launch_smo<8, CH, 512>(args, grid, smem, stream);
     }
 }
 
-static cudaError_t launch_smo_any(int Q, int CH, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+static cudaError_t launch_smo_any(int Q, int CH, int threads, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
 {
     switch (CH) {
-    case 1: return launch_smo_q<1>(Q, args, grid, smem, stream);
-    case 2: return launch_smo_q<2>(Q, args, grid, smem, stream);
-    default: return launch_smo_q<4>(Q, args, grid, smem, stream);
+    case 1: return launch_smo_q<1>(Q, threads, args, grid, smem, stream);
+    case 2: return launch_smo_q<2>(Q, threads, args, grid, smem, stream);
+    default: return launch_smo_q<4>(Q, threads, args, grid, smem, stream);
     }
 }
 
 template <int Q, int CH>
-static cudaError_t launch_decision(const float *Xq, long long m, const float *SV, const double *coef, int nsv, int pitch4,
+static cudaError_t launch_decision(const float *Xq, long long m, const float *SV, const double *svn, const double *coef, int nsv, int pitch4,
                                    double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
 {
     const size_t smem = decision_smem_bytes(pitch4);
     cudaError_t e = cudaFuncSetAttribute(decision_kernel<Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int grid = (int)((m + DEC_WARPS - 1) / DEC_WARPS);
-    decision_kernel<Q, CH><<<grid, DEC_THREADS, smem, stream>>>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out);
+    decision_kernel<Q, CH><<<grid, DEC_THREADS, smem, stream>>>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out);
     return cudaGetLastError();
 }
 
 template <int CH>
-static cudaError_t launch_decision_q(int Q, const float *Xq, long long m, const float *SV, const double *coef, int nsv,
+static cudaError_t launch_decision_q(int Q, const float *Xq, long long m, const float *SV, const double *svn, const double *coef, int nsv,
                                      int pitch4, double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
 {
     switch (Q) {
-    case 1: return launch_decision<1, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 2: return launch_decision<2, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 4: return launch_decision<4, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 7: return launch_decision<7, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    default: return launch_decision<8, CH>(Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 1: return launch_decision<1, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 2: return launch_decision<2, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 4: return launch_decision<4, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 7: return launch_decision<7, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    default: return launch_decision<8, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
     }
 }
 
-static cudaError_t launch_decision_any(int Q, int CH, const float *Xq, long long m, const float *SV, const double *coef,
+static cudaError_t launch_decision_any(int Q, int CH, const float *Xq, long long m, const float *SV, const double *svn, const double *coef,
                                        int nsv, int pitch4, double gamma, double init, const int *ysub, double *out,
                                        cudaStream_t stream)
 {
     switch (CH) {
-    case 1: return launch_decision_q<1>(Q, Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 2: return launch_decision_q<2>(Q, Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    default: return launch_decision_q<4>(Q, Xq, m, SV, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 1: return launch_decision_q<1>(Q, Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    case 2: return launch_decision_q<2>(Q, Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
+    default: return launch_decision_q<4>(Q, Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
     }
 }
 
 template <int Q, int CH>
-static cudaError_t launch_krow(const float *X, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
+static cudaError_t launch_krow(const float *X, const double *sqn, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
 {
     const long long threads = n * 32;
-    kernel_row_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, n, pitch4, pivot, gamma, out);
+    kernel_row_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, sqn, n, pitch4, pivot, gamma, out);
     return cudaGetLastError();
 }
 template <int CH>
-static cudaError_t launch_krow_q(int Q, const float *X, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
+static cudaError_t launch_krow_q(int Q, const float *X, const double *sqn, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
 {
     switch (Q) {
-    case 1: return launch_krow<1, CH>(X, n, pitch4, pivot, gamma, out, s);
-    case 2: return launch_krow<2, CH>(X, n, pitch4, pivot, gamma, out, s);
-    case 4: return launch_krow<4, CH>(X, n, pitch4, pivot, gamma, out, s);
-    case 7: return launch_krow<7, CH>(X, n, pitch4, pivot, gamma, out, s);
-    default: return launch_krow<8, CH>(X, n, pitch4, pivot, gamma, out, s);
+    case 1: return launch_krow<1, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
+    case 2: return launch_krow<2, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
+    case 4: return launch_krow<4, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
+    case 7: return launch_krow<7, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
+    default: return launch_krow<8, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
     }
 }
 
-static const int DEFAULT_CHUNK = 1;
+template <int Q, int CH>
+static cudaError_t launch_sqnorm(const float *X, long long n, int pitch4, double *sqn, cudaStream_t s)
+{
+    const long long threads = n * 32;
+    row_sqnorm_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, n, pitch4, sqn);
+    return cudaGetLastError();
+}
+template <int CH>
+static cudaError_t launch_sqnorm_q(int Q, const float *X, long long n, int pitch4, double *sqn, cudaStream_t s)
+{
+    switch (Q) {
+    case 1: return launch_sqnorm<1, CH>(X, n, pitch4, sqn, s);
+    case 2: return launch_sqnorm<2, CH>(X, n, pitch4, sqn, s);
+    case 4: return launch_sqnorm<4, CH>(X, n, pitch4, sqn, s);
+    case 7: return launch_sqnorm<7, CH>(X, n, pitch4, sqn, s);
+    default: return launch_sqnorm<8, CH>(X, n, pitch4, sqn, s);
+    }
+}
+static int q_for_pitch(int pitch4);
+// squared norms of the training rows for accumulation chunk CH (recomputed only when CH changes)
+static int ensure_norms(svmb200_ctx *ctx, int CH)
+{
+    if (ctx->sqn_chunk == CH) return 0;
+    const int Q = q_for_pitch(ctx->pitch4);
+    cudaError_t e;
+    switch (CH) {
+    case 1: e = launch_sqnorm_q<1>(Q, ctx->X, ctx->n, ctx->pitch4, ctx->sqn, ctx->stream); break;
+    case 2: e = launch_sqnorm_q<2>(Q, ctx->X, ctx->n, ctx->pitch4, ctx->sqn, ctx->stream); break;
+    default: e = launch_sqnorm_q<4>(Q, ctx->X, ctx->n, ctx->pitch4, ctx->sqn, ctx->stream); break;
+    }
+    ctx->launches += 1;
+    CK(e);
+    ctx->sqn_chunk = CH;
+    return 0;
+}
+
+static const int SMO_DEFAULT_THREADS_Q7 = 512;
+static const int DEFAULT_CHUNK = 4;   // fp32 storage of X dominates the error of K for every chunk (DESIGN.md "Numerics")
 
 static int resolve_chunk(int c)
 {
@@ -379,10 +439,11 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
 {
     const int nsv = (int)ids.size();
     if (nsv > ctx->sv_alloc) {
-        if (dev_free(ctx, ctx->svX) || dev_free(ctx, ctx->svcoef)) return SVMB200_ECUDA;
+        if (dev_free(ctx, ctx->svX) || dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn)) return SVMB200_ECUDA;
         const int cap = std::max(nsv, 1024);
         CK(cudaMalloc(&ctx->svX, (size_t)cap * ctx->pitch4 * 16));
         CK(cudaMalloc(&ctx->svcoef, (size_t)cap * sizeof(double)));
+        CK(cudaMalloc(&ctx->svn, (size_t)cap * sizeof(double)));
         ctx->sv_alloc = cap;
     }
     if (nsv == 0) return 0;
@@ -393,7 +454,7 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
     CK(cudaMemcpyAsync(ctx->svcoef, coef.data(), (size_t)nsv * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     const long long total = (long long)nsv * ctx->pitch4;
     gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
-        ctx->X, ctx->pitch4, static_cast<const int *>(ctx->scratch), nsv, ctx->svX);
+        ctx->X, ctx->sqn, ctx->pitch4, static_cast<const int *>(ctx->scratch), nsv, ctx->svX, ctx->svn);
     ctx->launches += 1;
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));   // coef / ids are host temporaries
@@ -415,9 +476,19 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 
     // persistent grid: one CTA per SM, fewer for tiny problems
     const int Q = q_for_pitch(ctx->pitch4);
+    int threads = 512;
+    if (Q == 7) {
+        threads = SMO_DEFAULT_THREADS_Q7;
+        if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py
+            const int t = atoi(e);
+            if (t == 256 || t == 384 || t == 512) threads = t;
+        }
+    }
+    const int warps = threads / 32;
     int kslots = SMO_KSLOTS_MAX;
-    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots) > (size_t)ctx->max_smem_optin) --kslots;
-    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots);
+    if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
+    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps) > (size_t)ctx->max_smem_optin) --kslots;
+    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
     const int grid = (int)std::max<long long>(1, std::min<long long>(ctx->num_sms, (n + 7) / 8));
 
@@ -437,7 +508,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 
     if (grid > ctx->rec_blocks) {
         if (dev_free(ctx, ctx->rec)) return SVMB200_ECUDA;
-        CK(cudaMalloc(&ctx->rec, (size_t)2 * grid * sizeof(Rec)));
+        CK(cudaMalloc(&ctx->rec, (size_t)2 * grid * sizeof(Rec) + 256));
         ctx->rec_blocks = grid;
     }
     const int trace_cap = std::max(0, params->trace_cap);
@@ -448,7 +519,8 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
 
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    CK(cudaMemsetAsync(ctx->rec, 0, (size_t)2 * ctx->rec_blocks * sizeof(Rec), ctx->stream));
+    if (int rc = ensure_norms(ctx, CH)) return rc;
+    CK(cudaMemsetAsync(ctx->rec, 0, (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 256, ctx->stream));
     if (params->warm_start) {
         // f_i = sum_{alpha_j != 0} alpha_j y_j K(x_j, x_i) - y_i   (mpi_svm_main2.cpp:169-183)
         CK(cudaMemcpyAsync(ctx->alpha, alpha, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
@@ -462,7 +534,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 0, 0);
         ctx->launches += 1;
         CK(cudaGetLastError());
-        CK(launch_decision_any(Q, CH, ctx->X, n, ctx->svX, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
+        CK(launch_decision_any(Q, CH, ctx->X, n, ctx->svX, ctx->svn, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
                                ctx->y, ctx->f, ctx->stream));
         ctx->launches += 1;
     } else {
@@ -472,9 +544,10 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
 
     SmoArgs a{};
-    a.X = ctx->X; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
+    a.X = ctx->X; a.sqn = ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
     a.cacheq = cache_cap > 0 ? ctx->cacheq : nullptr;
-    a.cacheK = ctx->cacheK; a.rec = ctx->rec; a.trace = ctx->trace; a.result = ctx->result;
+    a.cacheK = ctx->cacheK; a.rec = ctx->rec;
+    a.arrive = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
     a.n = n; a.pitch4 = ctx->pitch4; a.kslots = kslots; a.cache_cap = cache_cap; a.trace_cap = trace_cap;
     a.max_iter = params->max_iter;
     a.C = params->C; a.gamma = params->gamma; a.eps = params->eps; a.tau = params->tau;
@@ -489,9 +562,19 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         else if (persist) a.keep_per_1024 = (int)(1024.0 * l2_keep_budget / x_bytes);
     }
     a.peers = 1; a.rank = 0; a.row_begin = 0; a.row_end = n; a.mailbox = nullptr;
+    a.timing = nullptr; a.timing_cap = 0;
+#ifdef SVM_TIMING
+    {
+        static long long *tbuf = nullptr;
+        if (!tbuf) CK(cudaMalloc(&tbuf, (4096 * 8 + 8 * 160 * 4) * sizeof(long long)));
+        CK(cudaMemsetAsync(tbuf, 0, (4096 * 8 + 8 * 160 * 4) * sizeof(long long), ctx->stream));
+        a.timing = tbuf; a.timing_cap = 4096;
+        g_timing_dev = tbuf;
+    }
+#endif
 
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(launch_smo_any(Q, CH, a, grid, smem, ctx->stream));
+    CK(launch_smo_any(Q, CH, threads, a, grid, smem, ctx->stream));
     ctx->launches += 1;
     CK(cudaEventRecord(ctx->ev2, ctx->stream));
 
@@ -562,6 +645,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     CK(cudaStreamSynchronize(ctx->stream));
     std::vector<int> svy(ctx->sv_ids.size());
     for (size_t k = 0; k < svy.size(); ++k) svy[k] = y_host[ctx->sv_ids[k]];
+    if (int rc = ensure_norms(ctx, ctx->params.accum_chunk)) return rc;
     if (int rc = build_sv_block(ctx, ctx->sv_ids, ctx->alpha_host.data(), svy)) return rc;
 
     float *Xq = nullptr;
@@ -574,7 +658,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     int rc = ingest<T>(ctx, X, m, false, scale, Xq);
     cudaError_t e = cudaSuccess;
     if (!rc) {
-        e = launch_decision_any(q_for_pitch(pitch4), ctx->params.accum_chunk, Xq, m, ctx->svX, ctx->svcoef, (int)ctx->sv_ids.size(),
+        e = launch_decision_any(q_for_pitch(pitch4), ctx->params.accum_chunk, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, (int)ctx->sv_ids.size(),
                                 pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores, ctx->stream);
         ctx->launches += 1;
     }
@@ -643,14 +727,15 @@ int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_
     const int CH = resolve_chunk(accum_chunk);
     if (CH < 0) FAIL(SVMB200_EINVAL, "accum_chunk must be 0, 1, 2 or 4");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = ensure_norms(ctx, CH)) return rc;
     if (int rc = ensure_scratch(ctx, (size_t)ctx->n * sizeof(double))) return rc;
     double *out = static_cast<double *>(ctx->scratch);
     const int Q = q_for_pitch(ctx->pitch4);
     cudaError_t e;
     switch (CH) {
-    case 1: e = launch_krow_q<1>(Q, ctx->X, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
-    case 2: e = launch_krow_q<2>(Q, ctx->X, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
-    default: e = launch_krow_q<4>(Q, ctx->X, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
+    case 1: e = launch_krow_q<1>(Q, ctx->X, ctx->sqn, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
+    case 2: e = launch_krow_q<2>(Q, ctx->X, ctx->sqn, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
+    default: e = launch_krow_q<4>(Q, ctx->X, ctx->sqn, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
     }
     ctx->launches += 1;
     CK(e);

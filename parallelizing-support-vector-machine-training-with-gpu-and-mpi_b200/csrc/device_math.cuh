@@ -1,11 +1,12 @@
 // device_math.cuh -- arithmetic shared by every kernel of the path.
 //
 // The RBF kernel value replaces the reference's kernel() (code/main3.cpp:92-104).  The reference
-// sums 784 FP64 squared differences sequentially; here a warp owns one row, lane l takes the
-// float4 groups q = l, l+32, ... of the fp32 row, sums the squares of CH consecutive elements in
-// fp32 (fmaf), widens to FP64 and accumulates per lane, then the 32 lane sums are combined with
-// an xor-butterfly (16,8,4,2,1).  That order is fixed, so K(i,j) is bit-reproducible and the CPU
-// checker (oracle/smo_oracle.c, ORACLE_ARITH_DEVICE) restates it op for op.
+// sums 784 FP64 squared differences sequentially; here K(i,j) = exp(-gamma * max(0, |xi|^2 + |xj|^2
+// - 2 xi.xj)) with the dot product formed by a warp: lane l takes the float4 groups q = l, l+32, ...
+// of the fp32 rows, sums the products of CH consecutive elements in fp32 (fmaf), widens to FP64 and
+// accumulates per lane, then the 32 lane sums are combined with an xor-butterfly (16,8,4,2,1); the
+// squared norms are dot products of a row with itself.  That order is fixed, so K(i,j) is
+// bit-reproducible and the CPU checker (oracle/smo_oracle.c, ORACLE_ARITH_DEVICE) restates it op for op.
 //
 // Built with -fmad=false: every contraction in this library is an explicit fma()/fmaf(), so the
 // FP64 scalar update rounds exactly like the reference's x86-64 build (no FMA).
@@ -50,30 +51,30 @@ __device__ __forceinline__ double svm_exp(double x)
     return (p * s1) * s2;
 }
 
-// squares of one float4 group against the pivot's group, added to the lane's FP64 sum
+// products of one float4 group of a row with the same group of a pivot row, added to the lane's
+// FP64 sum.  CH = how many fp32 products are summed in fp32 before widening (CH = 1: every product
+// is exact in FP64).
 template <int CH>
-__device__ __forceinline__ void accum_sq(const float4 &v, const float4 &p, double &acc)
+__device__ __forceinline__ void accum_dot(const float4 &v, const float4 &p, double &acc)
 {
-    const float dx = v.x - p.x, dy = v.y - p.y, dz = v.z - p.z, dw = v.w - p.w;
     if (CH == 4) {
-        float s = dx * dx;
-        s = fmaf(dy, dy, s);
-        s = fmaf(dz, dz, s);
-        s = fmaf(dw, dw, s);
+        float s = v.x * p.x;
+        s = fmaf(v.y, p.y, s);
+        s = fmaf(v.z, p.z, s);
+        s = fmaf(v.w, p.w, s);
         acc = acc + (double)s;
     } else if (CH == 2) {
-        float s = dx * dx;
-        s = fmaf(dy, dy, s);
+        float s = v.x * p.x;
+        s = fmaf(v.y, p.y, s);
         acc = acc + (double)s;
-        float t = dz * dz;
-        t = fmaf(dw, dw, t);
+        float t = v.z * p.z;
+        t = fmaf(v.w, p.w, t);
         acc = acc + (double)t;
     } else {
-        double e;
-        e = (double)dx; acc = fma(e, e, acc);
-        e = (double)dy; acc = fma(e, e, acc);
-        e = (double)dz; acc = fma(e, e, acc);
-        e = (double)dw; acc = fma(e, e, acc);
+        acc = fma((double)v.x, (double)p.x, acc);
+        acc = fma((double)v.y, (double)p.y, acc);
+        acc = fma((double)v.z, (double)p.z, acc);
+        acc = fma((double)v.w, (double)p.w, acc);
     }
 }
 
@@ -82,6 +83,31 @@ __device__ __forceinline__ double warp_sum_butterfly(double v)
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) v = v + __shfl_xor_sync(FULL, v, off);
     return v;
+}
+
+// Two butterflies for the price of one and a bit: after the first exchange the lower half-warp
+// carries value a and the upper half value b; each half then finishes its own butterfly.  Every lane
+// forms exactly the sums the plain xor-butterfly forms (x + y == y + x), so the results are the same
+// bits.  On return a and b hold the two totals in every lane.
+__device__ __forceinline__ void warp_sum_butterfly2(double &a, double &b, int lane)
+{
+    const bool upper = (lane & 16) != 0;
+    const double send = upper ? a : b;
+    const double keep = upper ? b : a;
+    double v = keep + __shfl_xor_sync(FULL, send, 16);
+#pragma unroll
+    for (int off = 8; off >= 1; off >>= 1) v = v + __shfl_xor_sync(FULL, v, off);
+    const double other = __shfl_xor_sync(FULL, v, 16);
+    a = upper ? other : v;
+    b = upper ? v : other;
+}
+
+// squared distance from squared norms and the dot product, clamped at 0 (duplicates give exactly 0:
+// the norm of a row is its dot product with itself, formed by the same code)
+__device__ __forceinline__ double sqdist_from_dot(double na, double nb, double ab)
+{
+    const double s = (na + nb) - 2.0 * ab;
+    return s < 0.0 ? 0.0 : s;
 }
 
 // (value, lowest index) ordering of calc_i_high / calc_i_low (code/main3.cpp:113-120,132-139):

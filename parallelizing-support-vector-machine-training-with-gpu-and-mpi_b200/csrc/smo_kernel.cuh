@@ -27,24 +27,10 @@
 
 namespace svm {
 
-constexpr int SMO_THREADS = 512;          // 16 warps
-constexpr int SMO_WARPS = SMO_THREADS / 32;
-constexpr int SMO_KSLOTS_MAX = 4;         // ring depth per warp: 16 x 4 x 3136 B = 196 KB in flight per SM
+constexpr int SMO_MAX_WARPS = 16;         // the CTA size is a template parameter (256 / 384 / 512 threads)
+constexpr int SMO_KSLOTS_MAX = 8;         // ring depth per warp, sized so that warps x depth x row fills shared memory
 
-struct __align__(16) Cand {               // one side of a record: 32 bytes
-    double f;
-    double alpha;
-    long long q;                          // row-cache allocation number of the row, -1 = never cached
-    int idx;
-    int y;
-};
-
-struct __align__(128) Rec {               // one CTA's (or one GPU's) candidates for one exchange
-    Cand lo;                              // argmin f over I_high  -> i_high
-    Cand hi;                              // argmax f over I_low   -> i_low
-    int seq;                              // exchange number + 1, written last with release
-    int pad[15];
-};
+struct Rec;   // one CTA's candidates for one exchange; defined with the exchange below
 
 struct SmoResult {
     int num_iter;
@@ -58,12 +44,14 @@ struct SmoResult {
 
 struct SmoArgs {
     const float *X;        // [n][pitch4*4] fp32, zero padded
+    const double *sqn;     // [n] squared norms |x_j|^2 (dot product of the row with itself)
     const int *y;          // +-1
     double *f;
     double *alpha;
     long long *cacheq;     // per row: allocation number of its cached kernel row, or -1
     double *cacheK;        // [cache_cap][n] FP64 kernel rows
     Rec *rec;              // [2][grid]
+    unsigned *arrive;      // arrival counter of the record exchange (zeroed before the launch)
     int *trace;            // [trace_cap][2]
     SmoResult *result;
     long long n;
@@ -82,6 +70,8 @@ struct SmoArgs {
     long long row_begin, row_end;       // rows owned by this GPU (X is replicated, state is global-sized)
     Rec *mailbox;                       // [2][peers] local mailbox written by peers
     Rec *peer_mailbox[8];               // peers' mailboxes (peer-mapped device pointers)
+    long long *timing;                  // optional [iterations][8] clock64 stamps of CTA 0 (profiling builds only)
+    int timing_cap;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -92,8 +82,8 @@ struct Pivots {
 };
 
 template <int Q, int CH>
-__device__ __forceinline__ void row_sqdist2(const float4 *__restrict__ row, const Pivots<Q> &pv, int pitch4, int lane,
-                                            double &dh, double &dl)
+__device__ __forceinline__ void row_dot2(const float4 *__restrict__ row, const Pivots<Q> &pv, int pitch4, int lane,
+                                         double &dh, double &dl)
 {
     double ah = 0.0, al = 0.0;
 #pragma unroll
@@ -101,12 +91,13 @@ __device__ __forceinline__ void row_sqdist2(const float4 *__restrict__ row, cons
         const int q = i * 32 + lane;
         if (q < pitch4) {
             const float4 v = row[q];
-            accum_sq<CH>(v, pv.h[i], ah);
-            accum_sq<CH>(v, pv.l[i], al);
+            accum_dot<CH>(v, pv.h[i], ah);
+            accum_dot<CH>(v, pv.l[i], al);
         }
     }
-    dh = warp_sum_butterfly(ah);
-    dl = warp_sum_butterfly(al);
+    warp_sum_butterfly2(ah, al, lane);
+    dh = ah;
+    dl = al;
 }
 
 // membership tests of calc_i_high / calc_i_low (code/main3.cpp:115,134)
@@ -119,127 +110,190 @@ __device__ __forceinline__ bool in_I_low(int y, double a, double C, double eps)
     return (y == 1 && a > 0.0 + eps) || (y == -1 && a < C - eps);
 }
 
-struct LocalBest {
-    double fmin; int imin;
-    double fmax; int imax;
-};
 constexpr int IDX_NONE = 0x7fffffff;
+
+// A candidate for one side of the working pair, carried with everything the scalar update needs
+// from that row (main3.cpp:235,246,259 read y and alpha of the pair), so that no CTA ever has to
+// read another CTA's rows of alpha / y / cache bookkeeping.
+struct Best {
+    double f;
+    double alpha;
+    long long q;      // row-cache allocation number of the row, -1 = never cached
+    int idx;
+    int y;
+};
+struct LocalBest {
+    Best lo;          // argmin f over I_high  -> i_high
+    Best hi;          // argmax f over I_low   -> i_low
+};
 
 __device__ __forceinline__ void best_init(LocalBest &b)
 {
-    b.fmin = __longlong_as_double(0x7ff0000000000000LL);
-    b.imin = IDX_NONE;
-    b.fmax = __longlong_as_double(0xfff0000000000000LL);
-    b.imax = IDX_NONE;
+    b.lo.f = __longlong_as_double(0x7ff0000000000000LL);
+    b.hi.f = __longlong_as_double(0xfff0000000000000LL);
+    b.lo.idx = b.hi.idx = IDX_NONE;
+    b.lo.alpha = b.hi.alpha = 0.0;
+    b.lo.y = b.hi.y = 0;
+    b.lo.q = b.hi.q = -1;
 }
-__device__ __forceinline__ void best_merge(LocalBest &b, double fmin, int imin, double fmax, int imax)
+// a row joins the running argmin / argmax (ascending j per thread + strict compare = lowest index)
+__device__ __forceinline__ void best_consider(LocalBest &b, long long j, double fj, double aj, int yj, long long qj,
+                                              double C, double eps)
 {
-    if (better_min(fmin, imin, b.fmin, b.imin)) { b.fmin = fmin; b.imin = imin; }
-    if (better_max(fmax, imax, b.fmax, b.imax)) { b.fmax = fmax; b.imax = imax; }
+    if (in_I_high(yj, aj, C, eps) && fj < b.lo.f) { b.lo.f = fj; b.lo.idx = (int)j; b.lo.alpha = aj; b.lo.y = yj; b.lo.q = qj; }
+    if (in_I_low(yj, aj, C, eps) && fj > b.hi.f) { b.hi.f = fj; b.hi.idx = (int)j; b.hi.alpha = aj; b.hi.y = yj; b.hi.q = qj; }
+}
+template <bool IS_MIN>
+__device__ __forceinline__ bool best_better(double fa, int ia, double fb, int ib)
+{
+    return IS_MIN ? better_min(fa, ia, fb, ib) : better_max(fa, ia, fb, ib);
+}
+// warp-wide (value, lowest index) winner; every lane returns the winner with its payload
+template <bool IS_MIN>
+__device__ __forceinline__ void best_warp_one(Best &b)
+{
+    double f = b.f;
+    int idx = b.idx;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const double f2 = __shfl_xor_sync(FULL, f, off);
+        const int i2 = __shfl_xor_sync(FULL, idx, off);
+        if (best_better<IS_MIN>(f2, i2, f, idx)) { f = f2; idx = i2; }
+    }
+    const unsigned holders = __ballot_sync(FULL, b.idx == idx);   // a row index lives in exactly one lane
+    const int src = __ffs(holders) - 1;
+    b.alpha = __shfl_sync(FULL, b.alpha, src);
+    b.q = __shfl_sync(FULL, b.q, src);
+    b.y = __shfl_sync(FULL, b.y, src);
+    b.f = f;
+    b.idx = idx;
 }
 __device__ __forceinline__ void best_warp_reduce(LocalBest &b)
 {
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const double f1 = __shfl_xor_sync(FULL, b.fmin, off);
-        const int i1 = __shfl_xor_sync(FULL, b.imin, off);
-        const double f2 = __shfl_xor_sync(FULL, b.fmax, off);
-        const int i2 = __shfl_xor_sync(FULL, b.imax, off);
-        best_merge(b, f1, i1, f2, i2);
-    }
+    best_warp_one<true>(b.lo);
+    best_warp_one<false>(b.hi);
+}
+__device__ __forceinline__ void best_merge(LocalBest &b, const Best &lo, const Best &hi)
+{
+    if (better_min(lo.f, lo.idx, b.lo.f, b.lo.idx)) b.lo = lo;
+    if (better_max(hi.f, hi.idx, b.hi.f, b.hi.idx)) b.hi = hi;
+}
+
+// ---- the record exchange ---------------------------------------------------------------------
+// Every CTA stores its 64-byte record, then adds 1 to an arrival counter with release semantics.
+// ONE thread per CTA spins on the counter (148 pollers of one 4-byte word: no L2 queueing, unlike
+// 148 x 148 pollers of the records themselves, which measured ~10 us per exchange); when the
+// count is complete the CTA reads all records once, thread t taking CTA t's.
+struct __align__(64) Rec {
+    Best lo;
+    Best hi;
+};
+
+__device__ __forceinline__ void red_release_gpu_add(unsigned *p, unsigned v)
+{
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// 32-byte L1-bypassing load of one side of a record
+__device__ __forceinline__ Best ld_best_gpu(const Best *p)
+{
+    unsigned long long w0, w1, w2, w3;
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(reinterpret_cast<const char *>(p) + 16) : "memory");
+    Best b;
+    b.f = __longlong_as_double((long long)w0);
+    b.alpha = __longlong_as_double((long long)w1);
+    b.q = (long long)w2;
+    b.idx = (int)(w3 & 0xffffffffull);
+    b.y = (int)(w3 >> 32);
+    return b;
 }
 
 struct __align__(16) Shared {
-    Cand sel_lo, sel_hi;                  // the grid-wide winners of the last exchange
-    double wfmin[SMO_WARPS], wfmax[SMO_WARPS];
-    int wimin[SMO_WARPS], wimax[SMO_WARPS];
+    Best wlo[SMO_MAX_WARPS], whi[SMO_MAX_WARPS];  // per-warp winners of this CTA's rows
+    Best glo[SMO_MAX_WARPS], ghi[SMO_MAX_WARPS];  // per-warp winners over the gathered records
 };
 
-// One exchange: CTA-level reduce of the per-thread candidates, publish, gather, broadcast in smem.
-// Returns with sh.sel_lo / sh.sel_hi valid for every thread of the CTA.
+#ifdef SVM_TIMING
+#define SVM_STAMP(k) do { if (a.timing && blockIdx.x == 0 && threadIdx.x == 0 && gather_no < a.timing_cap) a.timing[(size_t)gather_no * 8 + (k)] = clock64(); } while (0)
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define SVM_GSTAMP(k) do { if (a.timing && threadIdx.x == 0 && gather_no >= 100 && gather_no < 108) a.timing[(size_t)a.timing_cap * 8 + ((size_t)(gather_no - 100) * gridDim.x + blockIdx.x) * 4 + (k)] = (long long)gtimer(); } while (0)
+#else
+#define SVM_STAMP(k) do { } while (0)
+#define SVM_GSTAMP(k) do { } while (0)
+#endif
+
+// One exchange: CTA-level reduce of the per-thread candidates, publish, gather.  On return every
+// thread of every CTA holds the same grid-wide winners in `mine`.
 __device__ __forceinline__ void exchange(const SmoArgs &a, Shared &sh, LocalBest &mine, int gather_no)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x;
+    const int nwarps = (int)(blockDim.x >> 5);
     best_warp_reduce(mine);
-    if (lane == 0) {
-        sh.wfmin[warp] = mine.fmin; sh.wimin[warp] = mine.imin;
-        sh.wfmax[warp] = mine.fmax; sh.wimax[warp] = mine.imax;
-    }
+    if (lane == 0) { sh.wlo[warp] = mine.lo; sh.whi[warp] = mine.hi; }
+    SVM_STAMP(3);
     __syncthreads();
+    SVM_STAMP(4);
+    Rec *recs = a.rec + (size_t)(gather_no & 1) * G;
     if (warp == 0) {
         LocalBest b;
         best_init(b);
-        if (lane < SMO_WARPS) { b.fmin = sh.wfmin[lane]; b.imin = sh.wimin[lane]; b.fmax = sh.wfmax[lane]; b.imax = sh.wimax[lane]; }
+        if (lane < nwarps) { b.lo = sh.wlo[lane]; b.hi = sh.whi[lane]; }
         best_warp_reduce(b);
-        Rec *mine_rec = a.rec + (size_t)(gather_no & 1) * G + blockIdx.x;
         if (lane == 0) {
-            Cand lo, hi;
-            lo.f = b.fmin; lo.idx = b.imin; lo.alpha = 0.0; lo.y = 0; lo.q = -1;
-            hi.f = b.fmax; hi.idx = b.imax; hi.alpha = 0.0; hi.y = 0; hi.q = -1;
-            if (b.imin != IDX_NONE) { lo.alpha = a.alpha[b.imin]; lo.y = a.y[b.imin]; lo.q = a.cacheq ? a.cacheq[b.imin] : -1; }
-            if (b.imax != IDX_NONE) { hi.alpha = a.alpha[b.imax]; hi.y = a.y[b.imax]; hi.q = a.cacheq ? a.cacheq[b.imax] : -1; }
-            mine_rec->lo = lo;
-            mine_rec->hi = hi;
-            st_release_gpu(&mine_rec->seq, gather_no + 1);
-        }
-        // gather: lane l acquires the records of CTAs l, l+32, ...
-        LocalBest g;
-        best_init(g);
-        int bmin = -1, bmax = -1;
-        for (int c = lane; c < G; c += 32) {
-            const Rec *r = a.rec + (size_t)(gather_no & 1) * G + c;
-            while (ld_acquire_gpu(&r->seq) != gather_no + 1) { }
-            const double f1 = r->lo.f; const int i1 = r->lo.idx;
-            const double f2 = r->hi.f; const int i2 = r->hi.idx;
-            if (better_min(f1, i1, g.fmin, g.imin)) { g.fmin = f1; g.imin = i1; bmin = c; }
-            if (better_max(f2, i2, g.fmax, g.imax)) { g.fmax = f2; g.imax = i2; bmax = c; }
-        }
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) {
-            const double f1 = __shfl_xor_sync(FULL, g.fmin, off);
-            const int i1 = __shfl_xor_sync(FULL, g.imin, off);
-            const int c1 = __shfl_xor_sync(FULL, bmin, off);
-            const double f2 = __shfl_xor_sync(FULL, g.fmax, off);
-            const int i2 = __shfl_xor_sync(FULL, g.imax, off);
-            const int c2 = __shfl_xor_sync(FULL, bmax, off);
-            if (better_min(f1, i1, g.fmin, g.imin)) { g.fmin = f1; g.imin = i1; bmin = c1; }
-            if (better_max(f2, i2, g.fmax, g.imax)) { g.fmax = f2; g.imax = i2; bmax = c2; }
-        }
-        if (lane == 0) {
-            Cand lo, hi;
-            lo.f = g.fmin; lo.idx = IDX_NONE; lo.alpha = 0.0; lo.y = 0; lo.q = -1;
-            hi.f = g.fmax; hi.idx = IDX_NONE; hi.alpha = 0.0; hi.y = 0; hi.q = -1;
-            if (bmin >= 0 && g.imin != IDX_NONE) lo = a.rec[(size_t)(gather_no & 1) * G + bmin].lo;
-            if (bmax >= 0 && g.imax != IDX_NONE) hi = a.rec[(size_t)(gather_no & 1) * G + bmax].hi;
-            sh.sel_lo = lo;
-            sh.sel_hi = hi;
+            recs[blockIdx.x].lo = b.lo;
+            recs[blockIdx.x].hi = b.hi;
+            red_release_gpu_add(a.arrive, 1u);
+            SVM_STAMP(5);
+            const unsigned target = (unsigned)G * ((unsigned)gather_no + 1u);
+            while ((int)(ld_acquire_gpu_u32(a.arrive) - target) < 0) { }
+            SVM_STAMP(6);
         }
     }
     __syncthreads();
+    // thread t reads the record of CTA t
+    const int gather_warps = (G + 31) >> 5;
+    if (warp < gather_warps) {
+        LocalBest g;
+        best_init(g);
+        if ((int)threadIdx.x < G) { g.lo = ld_best_gpu(&recs[threadIdx.x].lo); g.hi = ld_best_gpu(&recs[threadIdx.x].hi); }
+        best_warp_reduce(g);
+        if (lane == 0) { sh.glo[warp] = g.lo; sh.ghi[warp] = g.hi; }
+    }
+    __syncthreads();
+    best_init(mine);
+    for (int w = 0; w < gather_warps; ++w) best_merge(mine, sh.glo[w], sh.ghi[w]);
+    SVM_STAMP(7);
 }
 
 // ------------------------------------------------------------------------------------------
-template <int Q, int CH>
-__global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __grid_constant__ SmoArgs a)
+template <int Q, int CH, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid_constant__ SmoArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x;
+    constexpr int WARPS = THREADS / 32;
     const int row_bytes = a.pitch4 * 16;
     // shared-memory carve-up: [warps][slots] rows | mbarriers | Shared
     unsigned char *slots = smem_raw;
     const int KS = a.kslots;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + (size_t)SMO_WARPS * KS * row_bytes);
-    Shared &sh = *reinterpret_cast<Shared *>(bars + SMO_WARPS * SMO_KSLOTS_MAX);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + (size_t)WARPS * KS * row_bytes);
+    Shared &sh = *reinterpret_cast<Shared *>(bars + WARPS * SMO_KSLOTS_MAX);
 
     // rows owned by this CTA and, inside it, by this warp (contiguous ranges)
     const long long n_own = a.row_end - a.row_begin;
     const long long r0 = a.row_begin + (long long)blockIdx.x * n_own / G;
     const long long r1 = a.row_begin + (long long)(blockIdx.x + 1) * n_own / G;
     const long long R = r1 - r0;
-    const long long w0 = r0 + (long long)warp * R / SMO_WARPS;
-    const long long w1 = r0 + (long long)(warp + 1) * R / SMO_WARPS;
+    const long long w0 = r0 + (long long)warp * R / WARPS;
+    const long long w1 = r0 + (long long)(warp + 1) * R / WARPS;
     const int m = (int)(w1 - w0);
     const int keep_rows = (int)(((long long)m * a.keep_per_1024) >> 10);
 
@@ -252,30 +306,26 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
     __syncthreads();
 
     // the ring: rows of this warp's range are requested in order, cyclically, for ever
-    unsigned issued = 0, consumed = 0;   // row copies requested / used so far (mod 2^32 is fine)
+    // Each slot is refilled right after it is used, so "the slot to use next" is the whole state.
+    int cslot = 0;                       // slot holding the next row to use
+    unsigned cphase = 0;                 // mbarrier phase parity of that slot
     int pf_row = 0;                      // next row of the range to request
-    auto issue_one = [&]() {             // called by the whole warp (counters stay warp-uniform); lane 0 issues
+    auto issue_into = [&](int s) {       // called by the whole warp (state stays warp-uniform); lane 0 issues
         if (lane == 0) {
-            const int s = issued % KS;
             mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
             bulk_g2s(my_slots + (size_t)s * row_bytes, a.X + (size_t)(w0 + pf_row) * a.pitch4 * 4, (unsigned)row_bytes,
                      &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
         }
-        ++issued;
         if (++pf_row == m) pf_row = 0;
     };
     if (m > 0)
-        for (int s = 0; s < KS; ++s) issue_one();
+        for (int s = 0; s < KS; ++s) issue_into(s);
 
     // ---- exchange 0: selection over the initial state (main3.cpp:203-204 in the first iteration)
     LocalBest mine;
     best_init(mine);
-    for (long long j = r0 + threadIdx.x; j < r1; j += SMO_THREADS) {
-        const double fj = a.f[j], aj = a.alpha[j];
-        const int yj = a.y[j];
-        if (in_I_high(yj, aj, a.C, a.eps) && fj < mine.fmin) { mine.fmin = fj; mine.imin = (int)j; }
-        if (in_I_low(yj, aj, a.C, a.eps) && fj > mine.fmax) { mine.fmax = fj; mine.imax = (int)j; }
-    }
+    for (long long j = r0 + threadIdx.x; j < r1; j += THREADS)
+        best_consider(mine, j, a.f[j], a.alpha[j], a.y[j], a.cacheq ? a.cacheq[j] : -1, a.C, a.eps);
     int gather_no = 0;
     exchange(a, sh, mine, gather_no);
 
@@ -287,7 +337,9 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
     long long x_passes = 0, cache_hits = 0;
 
     for (;;) {
-        const Cand lo = sh.sel_lo, hi = sh.sel_hi;
+        const Best lo = mine.lo, hi = mine.hi;
+        SVM_STAMP(0);
+        SVM_GSTAMP(0);
         i_high = lo.idx == IDX_NONE ? a.n : lo.idx;
         i_low = hi.idx == IDX_NONE ? a.n : hi.idx;
         if (lo.idx == IDX_NONE || hi.idx == IDX_NONE) { stop = 1; break; }          // main3.cpp:205
@@ -306,7 +358,7 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
 
         // K12 = K(i_high, i_low)  (main3.cpp:241)
         Pivots<Q> pv;
-        double K12;
+        double K12, n_h = 0.0, n_l = 0.0;
         if (!use_cache) {
             const float4 *xh = reinterpret_cast<const float4 *>(a.X) + (size_t)i_high * a.pitch4;
             const float4 *xl = reinterpret_cast<const float4 *>(a.X) + (size_t)i_low * a.pitch4;
@@ -319,9 +371,11 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
             double acc = 0.0;
 #pragma unroll
             for (int i = 0; i < Q; ++i)
-                if (i * 32 + lane < a.pitch4) accum_sq<CH>(pv.l[i], pv.h[i], acc);
+                if (i * 32 + lane < a.pitch4) accum_dot<CH>(pv.l[i], pv.h[i], acc);
             acc = warp_sum_butterfly(acc);
-            K12 = svm_exp(-a.gamma * acc);
+            n_h = a.sqn[i_high];
+            n_l = a.sqn[i_low];
+            K12 = svm_exp(-a.gamma * sqdist_from_dot(n_h, n_l, acc));
         } else {
             K12 = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low];
         }
@@ -366,7 +420,10 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
             slot_l = (int)(q_l % a.cache_cap);
         }
 
-        best_init(mine);
+        LocalBest acc_best;
+        best_init(acc_best);
+        SVM_STAMP(1);
+        SVM_GSTAMP(1);
         if (!use_cache) {
             // ---------------- X pass: a warp per row ----------------
             ++x_passes;
@@ -376,31 +433,31 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
                 const long long j = w0 + base + lane;
                 double fj = 0.0, aj = 0.0;
                 int yj = 0;
-                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; }
+                long long qj = -1;
+                double nj = 0.0;
+                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; nj = a.sqn[j]; if (a.cacheq) qj = a.cacheq[j]; }
                 double my_dh = 0.0, my_dl = 0.0;
                 for (int t = 0; t < cnt; ++t) {
-                    const int sidx = consumed % KS;
-                    mbar_wait(&my_bars[sidx], (consumed / KS) & 1);
+                    mbar_wait(&my_bars[cslot], cphase);
                     double dh, dl;
-                    row_sqdist2<Q, CH>(reinterpret_cast<const float4 *>(my_slots + (size_t)sidx * row_bytes), pv, a.pitch4, lane, dh, dl);
-                    ++consumed;
+                    row_dot2<Q, CH>(reinterpret_cast<const float4 *>(my_slots + (size_t)cslot * row_bytes), pv, a.pitch4, lane, dh, dl);
                     if (lane == t) { my_dh = dh; my_dl = dl; }
                     // the slot is free again: request the next row of the ring into it
                     __syncwarp();
                     fence_proxy_async();
-                    issue_one();
+                    issue_into(cslot);
+                    if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
                 }
                 if (lane < cnt) {
-                    const double kh = svm_exp(-a.gamma * my_dh);
-                    const double kl = svm_exp(-a.gamma * my_dl);
+                    const double kh = svm_exp(-a.gamma * sqdist_from_dot(n_h, nj, my_dh));
+                    const double kl = svm_exp(-a.gamma * sqdist_from_dot(n_l, nj, my_dl));
                     fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
                     a.f[j] = fj;
                     if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
                     if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
-                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) a.cacheq[j] = q_h; }
-                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) a.cacheq[j] = q_l; }
-                    if (in_I_high(yj, aj, a.C, a.eps) && fj < mine.fmin) { mine.fmin = fj; mine.imin = (int)j; }
-                    if (in_I_low(yj, aj, a.C, a.eps) && fj > mine.fmax) { mine.fmax = fj; mine.imax = (int)j; }
+                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
+                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
+                    best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
                 }
             }
         } else {
@@ -408,19 +465,22 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
             ++cache_hits;
             const double *kh_row = a.cacheK + (size_t)slot_h * a.n;
             const double *kl_row = a.cacheK + (size_t)slot_l * a.n;
-            for (long long j = r0 + threadIdx.x; j < r1; j += SMO_THREADS) {
+            for (long long j = r0 + threadIdx.x; j < r1; j += THREADS) {
                 double fj = a.f[j], aj = a.alpha[j];
                 const int yj = a.y[j];
+                const long long qj = a.cacheq[j];
                 fj = fj + (c_h * kh_row[j] + c_l * kl_row[j]);
                 a.f[j] = fj;
                 if (j == i_high) { aj = na_h; a.alpha[j] = aj; }
                 if (j == i_low) { aj = na_l; a.alpha[j] = aj; }
-                if (in_I_high(yj, aj, a.C, a.eps) && fj < mine.fmin) { mine.fmin = fj; mine.imin = (int)j; }
-                if (in_I_low(yj, aj, a.C, a.eps) && fj > mine.fmax) { mine.fmax = fj; mine.imax = (int)j; }
+                best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
             }
         }
 
+        SVM_STAMP(2);
+        SVM_GSTAMP(2);
         ++gather_no;
+        mine = acc_best;
         exchange(a, sh, mine, gather_no);
 
         ++num_iter;                                              // main3.cpp:281-287
@@ -428,10 +488,11 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
     }
 
     // drain the ring: every requested copy must land before the CTA may exit
-    while (consumed != issued) {
-        mbar_wait(&my_bars[consumed % KS], (consumed / KS) & 1);
-        ++consumed;
-    }
+    if (m > 0)
+        for (int k = 0; k < KS; ++k) {
+            mbar_wait(&my_bars[cslot], cphase);
+            if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
+        }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         SmoResult r;
         r.num_iter = num_iter; r.stop_reason = stop;
@@ -442,9 +503,9 @@ __global__ void __launch_bounds__(SMO_THREADS, 1) smo_persistent_kernel(const __
     }
 }
 
-inline size_t smo_smem_bytes(int pitch4, int kslots)
+inline size_t smo_smem_bytes(int pitch4, int kslots, int warps)
 {
-    return (size_t)SMO_WARPS * kslots * pitch4 * 16 + sizeof(uint64_t) * SMO_WARPS * SMO_KSLOTS_MAX + sizeof(Shared) + 128;
+    return (size_t)warps * kslots * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128;
 }
 
 } // namespace svm

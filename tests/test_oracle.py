@@ -111,10 +111,10 @@ def test_device_arithmetic_restated(O):
             b = rng.uniform(0, 1, d).astype(np.float32)
             k = L.oracle_device_kernel(a, b, d, 0.00125)
             kr = L.oracle_kernel(a.astype(np.float64), b.astype(np.float64), d, 0.00125)
-            assert abs(k - kr) <= (2e-9 if ch == 1 else 2e-7) * kr
+            assert abs(k - kr) <= 2e-7 * kr
             assert L.oracle_device_kernel(a, a, d, 0.00125) == 1.0
             assert L.oracle_device_kernel(a, b, d, 0.00125) == L.oracle_device_kernel(b, a, d, 0.00125)
-    O.set_device_chunk(1)
+    O.set_device_chunk(O.DEFAULT_CHUNK)
 
 
 def test_selection_rules(O):
