@@ -22,12 +22,12 @@ static long long *g_timing_dev = nullptr;
 extern "C" int svmb200_debug_timing(long long *out, int rows)
 {
     if (!g_timing_dev) return -1;
-    return cudaMemcpy(out, g_timing_dev, (size_t)rows * 8 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
+    return cudaMemcpy(out, g_timing_dev, (size_t)rows * 16 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
 }
 extern "C" int svmb200_debug_timing_grid(long long *out)
 {
     if (!g_timing_dev) return -1;
-    return cudaMemcpy(out, g_timing_dev + 4096 * 8, (size_t)8 * 160 * 4 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
+    return cudaMemcpy(out, g_timing_dev + 4096 * 16, (size_t)8 * 160 * 4 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
 }
 #endif
 
@@ -485,7 +485,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         }
     }
     const int warps = threads / 32;
-    int kslots = SMO_KSLOTS_MAX;
+    // two rows per warp in flight (16 warps x 2 x 3136 B = 98 KB per SM) already saturate HBM; deeper
+    // rings only lengthen the queues the record exchange has to wait behind (profiles/r1_notes.md)
+    int kslots = 2;
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
     while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps) > (size_t)ctx->max_smem_optin) --kslots;
     const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps);
@@ -561,13 +563,15 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         if (x_bytes <= l2_keep_budget) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
         else if (persist) a.keep_per_1024 = (int)(1024.0 * l2_keep_budget / x_bytes);
     }
+    a.l2_ahead = 0;
+    if (const char *e = getenv("SVMB200_L2AHEAD")) a.l2_ahead = std::max(0, std::min(32, atoi(e)));
     a.peers = 1; a.rank = 0; a.row_begin = 0; a.row_end = n; a.mailbox = nullptr;
     a.timing = nullptr; a.timing_cap = 0;
 #ifdef SVM_TIMING
     {
         static long long *tbuf = nullptr;
-        if (!tbuf) CK(cudaMalloc(&tbuf, (4096 * 8 + 8 * 160 * 4) * sizeof(long long)));
-        CK(cudaMemsetAsync(tbuf, 0, (4096 * 8 + 8 * 160 * 4) * sizeof(long long), ctx->stream));
+        if (!tbuf) CK(cudaMalloc(&tbuf, (4096 * 16 + 8 * 160 * 4) * sizeof(long long)));
+        CK(cudaMemsetAsync(tbuf, 0, (4096 * 16 + 8 * 160 * 4) * sizeof(long long), ctx->stream));
         a.timing = tbuf; a.timing_cap = 4096;
         g_timing_dev = tbuf;
     }

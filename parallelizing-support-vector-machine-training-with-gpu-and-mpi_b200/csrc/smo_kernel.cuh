@@ -64,6 +64,7 @@ struct SmoArgs {
     unsigned long long policy_stream;  // L2 policy for the streamed part of every CTA's rows
     unsigned long long policy_keep;    // L2 policy for the leading keep_frac of every warp's rows
     int keep_per_1024;                 // rows (per 1024) of each warp's range loaded with policy_keep
+    int l2_ahead;                      // rows requested into L2 ahead of the shared-memory ring (0 = off)
     // ---- multi-GPU row sharding (peers == 1: single GPU) ----
     int peers;                          // GPUs sharing the rows
     int rank;                           // this GPU
@@ -143,30 +144,32 @@ __device__ __forceinline__ void best_consider(LocalBest &b, long long j, double 
     if (in_I_high(yj, aj, C, eps) && fj < b.lo.f) { b.lo.f = fj; b.lo.idx = (int)j; b.lo.alpha = aj; b.lo.y = yj; b.lo.q = qj; }
     if (in_I_low(yj, aj, C, eps) && fj > b.hi.f) { b.hi.f = fj; b.hi.idx = (int)j; b.hi.alpha = aj; b.hi.y = yj; b.hi.q = qj; }
 }
-template <bool IS_MIN>
-__device__ __forceinline__ bool best_better(double fa, int ia, double fb, int ib)
+// Warp-wide (value, lowest index) winner with the hardware integer reduction (REDUX): the double is
+// mapped to a 64-bit key whose unsigned order is the double's order, its two halves are reduced one
+// after the other, and the row index breaks ties.  f + 0.0 folds -0.0 into +0.0 so that, as in the
+// reference's "<" / ">" scans, the two zeros tie.  Every lane returns the winner with its payload.
+__device__ __forceinline__ unsigned long long order_key(double f)
 {
-    return IS_MIN ? better_min(fa, ia, fb, ib) : better_max(fa, ia, fb, ib);
+    const unsigned long long u = (unsigned long long)__double_as_longlong(f + 0.0);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
 }
-// warp-wide (value, lowest index) winner; every lane returns the winner with its payload
 template <bool IS_MIN>
 __device__ __forceinline__ void best_warp_one(Best &b)
 {
-    double f = b.f;
-    int idx = b.idx;
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) {
-        const double f2 = __shfl_xor_sync(FULL, f, off);
-        const int i2 = __shfl_xor_sync(FULL, idx, off);
-        if (best_better<IS_MIN>(f2, i2, f, idx)) { f = f2; idx = i2; }
-    }
-    const unsigned holders = __ballot_sync(FULL, b.idx == idx);   // a row index lives in exactly one lane
+    unsigned long long key = order_key(b.f);
+    if (!IS_MIN) key = ~key;
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mhi = __reduce_min_sync(FULL, hi);
+    const unsigned mlo = __reduce_min_sync(FULL, hi == mhi ? lo : 0xffffffffu);
+    const bool tie = hi == mhi && lo == mlo;
+    const unsigned midx = __reduce_min_sync(FULL, tie ? (unsigned)b.idx : 0xffffffffu);
+    const unsigned holders = __ballot_sync(FULL, tie && (unsigned)b.idx == midx);   // a row index lives in exactly one lane
     const int src = __ffs(holders) - 1;
+    b.f = __shfl_sync(FULL, b.f, src);
     b.alpha = __shfl_sync(FULL, b.alpha, src);
     b.q = __shfl_sync(FULL, b.q, src);
+    b.idx = __shfl_sync(FULL, b.idx, src);
     b.y = __shfl_sync(FULL, b.y, src);
-    b.f = f;
-    b.idx = idx;
 }
 __device__ __forceinline__ void best_warp_reduce(LocalBest &b)
 {
@@ -180,38 +183,88 @@ __device__ __forceinline__ void best_merge(LocalBest &b, const Best &lo, const B
 }
 
 // ---- the record exchange ---------------------------------------------------------------------
-// Every CTA stores its 64-byte record, then adds 1 to an arrival counter with release semantics.
-// ONE thread per CTA spins on the counter (148 pollers of one 4-byte word: no L2 queueing, unlike
-// 148 x 148 pollers of the records themselves, which measured ~10 us per exchange); when the
-// count is complete the CTA reads all records once, thread t taking CTA t's.
-struct __align__(64) Rec {
-    Best lo;
-    Best hi;
-};
+// Every CTA stores its record, then adds 1 to an arrival counter.  ONE thread per CTA spins on the
+// counter (148 pollers of one 4-byte word; having all 148 x 148 record readers spin instead measured
+// ~10 us per exchange in L2 queueing); when the count is complete thread t reads CTA t's record.
+// No fence orders the record against the counter.  Instead a record is 16 words of 8 bytes, each
+// {32 data bits, 32-bit exchange number}: an aligned 8-byte access is single-copy atomic, so a word
+// that shows the right number also shows its data, and a reader that is too early simply re-reads.
+constexpr int REC_WORDS = 16;
+struct __align__(128) Rec { unsigned long long w[REC_WORDS]; };
 
-__device__ __forceinline__ void red_release_gpu_add(unsigned *p, unsigned v)
+__device__ __forceinline__ unsigned rec_word(const LocalBest &b, int k)
 {
-    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    switch (k) {
+    case 0: return (unsigned)__double2loint(b.lo.f);
+    case 1: return (unsigned)__double2hiint(b.lo.f);
+    case 2: return (unsigned)b.lo.idx;
+    case 3: return (unsigned)__double2loint(b.hi.f);
+    case 4: return (unsigned)__double2hiint(b.hi.f);
+    case 5: return (unsigned)b.hi.idx;
+    case 6: return (unsigned)__double2loint(b.lo.alpha);
+    case 7: return (unsigned)__double2hiint(b.lo.alpha);
+    case 8: return (unsigned)__double2loint(b.hi.alpha);
+    case 9: return (unsigned)__double2hiint(b.hi.alpha);
+    case 10: return (unsigned)b.lo.y;
+    case 11: return (unsigned)b.hi.y;
+    case 12: return (unsigned)(b.lo.q & 0xffffffffLL);
+    case 13: return (unsigned)((unsigned long long)b.lo.q >> 32);
+    case 14: return (unsigned)(b.hi.q & 0xffffffffLL);
+    default: return (unsigned)((unsigned long long)b.hi.q >> 32);
+    }
 }
-__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned *p)
+__device__ __forceinline__ void rec_unpack(const unsigned long long (&w)[REC_WORDS], LocalBest &b)
+{
+    auto d = [&](int k) { return (unsigned)(w[k] & 0xffffffffull); };
+    b.lo.f = __hiloint2double((int)d(1), (int)d(0));
+    b.lo.idx = (int)d(2);
+    b.hi.f = __hiloint2double((int)d(4), (int)d(3));
+    b.hi.idx = (int)d(5);
+    b.lo.alpha = __hiloint2double((int)d(7), (int)d(6));
+    b.hi.alpha = __hiloint2double((int)d(9), (int)d(8));
+    b.lo.y = (int)d(10);
+    b.hi.y = (int)d(11);
+    b.lo.q = (long long)(((unsigned long long)d(13) << 32) | d(12));
+    b.hi.q = (long long)(((unsigned long long)d(15) << 32) | d(14));
+}
+template <bool SYS>
+__device__ __forceinline__ void rec_store(Rec *r, const LocalBest &b, unsigned seq)
+{
+#pragma unroll
+    for (int k = 0; k < REC_WORDS; k += 2) {
+        const unsigned long long v0 = ((unsigned long long)seq << 32) | rec_word(b, k);
+        const unsigned long long v1 = ((unsigned long long)seq << 32) | rec_word(b, k + 1);
+        if (SYS) asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
+        else asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
+    }
+}
+// read a record; re-read until all 16 words carry `seq`
+template <bool SYS>
+__device__ __forceinline__ void rec_read(const Rec *r, unsigned seq, LocalBest &out)
+{
+    unsigned long long w[REC_WORDS];
+    for (;;) {
+#pragma unroll
+        for (int k = 0; k < REC_WORDS; k += 2) {
+            if (SYS) asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[k]), "=l"(w[k + 1]) : "l"(&r->w[k]) : "memory");
+            else asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[k]), "=l"(w[k + 1]) : "l"(&r->w[k]) : "memory");
+        }
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < REC_WORDS; ++k) ok = ok && ((unsigned)(w[k] >> 32) == seq);
+        if (ok) break;
+    }
+    rec_unpack(w, out);
+}
+__device__ __forceinline__ void red_relaxed_gpu_add(unsigned *p, unsigned v)
+{
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_relaxed_gpu_u32(const unsigned *p)
 {
     unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
-}
-// 32-byte L1-bypassing load of one side of a record
-__device__ __forceinline__ Best ld_best_gpu(const Best *p)
-{
-    unsigned long long w0, w1, w2, w3;
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(reinterpret_cast<const char *>(p) + 16) : "memory");
-    Best b;
-    b.f = __longlong_as_double((long long)w0);
-    b.alpha = __longlong_as_double((long long)w1);
-    b.q = (long long)w2;
-    b.idx = (int)(w3 & 0xffffffffull);
-    b.y = (int)(w3 >> 32);
-    return b;
 }
 
 struct __align__(16) Shared {
@@ -220,9 +273,9 @@ struct __align__(16) Shared {
 };
 
 #ifdef SVM_TIMING
-#define SVM_STAMP(k) do { if (a.timing && blockIdx.x == 0 && threadIdx.x == 0 && gather_no < a.timing_cap) a.timing[(size_t)gather_no * 8 + (k)] = clock64(); } while (0)
+#define SVM_STAMP(k) do { if (a.timing && blockIdx.x == 0 && threadIdx.x == 0 && gather_no < a.timing_cap) a.timing[(size_t)gather_no * 16 + (k)] = clock64(); } while (0)
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define SVM_GSTAMP(k) do { if (a.timing && threadIdx.x == 0 && gather_no >= 100 && gather_no < 108) a.timing[(size_t)a.timing_cap * 8 + ((size_t)(gather_no - 100) * gridDim.x + blockIdx.x) * 4 + (k)] = (long long)gtimer(); } while (0)
+#define SVM_GSTAMP(k) do { if (a.timing && threadIdx.x == 0 && gather_no >= 100 && gather_no < 108) a.timing[(size_t)a.timing_cap * 16 + ((size_t)(gather_no - 100) * gridDim.x + blockIdx.x) * 4 + (k)] = (long long)gtimer(); } while (0)
 #else
 #define SVM_STAMP(k) do { } while (0)
 #define SVM_GSTAMP(k) do { } while (0)
@@ -235,6 +288,7 @@ __device__ __forceinline__ void exchange(const SmoArgs &a, Shared &sh, LocalBest
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x;
     const int nwarps = (int)(blockDim.x >> 5);
+    const unsigned seq = (unsigned)gather_no + 1u;
     best_warp_reduce(mine);
     if (lane == 0) { sh.wlo[warp] = mine.lo; sh.whi[warp] = mine.hi; }
     SVM_STAMP(3);
@@ -245,14 +299,16 @@ __device__ __forceinline__ void exchange(const SmoArgs &a, Shared &sh, LocalBest
         LocalBest b;
         best_init(b);
         if (lane < nwarps) { b.lo = sh.wlo[lane]; b.hi = sh.whi[lane]; }
+        SVM_STAMP(8);
         best_warp_reduce(b);
+        SVM_STAMP(9);
         if (lane == 0) {
-            recs[blockIdx.x].lo = b.lo;
-            recs[blockIdx.x].hi = b.hi;
-            red_release_gpu_add(a.arrive, 1u);
+            rec_store<false>(recs + blockIdx.x, b, seq);
+            SVM_STAMP(10);
+            red_relaxed_gpu_add(a.arrive, 1u);
             SVM_STAMP(5);
-            const unsigned target = (unsigned)G * ((unsigned)gather_no + 1u);
-            while ((int)(ld_acquire_gpu_u32(a.arrive) - target) < 0) { }
+            const unsigned target = (unsigned)G * seq;
+            while ((int)(ld_relaxed_gpu_u32(a.arrive) - target) < 0) { }
             SVM_STAMP(6);
         }
     }
@@ -262,13 +318,18 @@ __device__ __forceinline__ void exchange(const SmoArgs &a, Shared &sh, LocalBest
     if (warp < gather_warps) {
         LocalBest g;
         best_init(g);
-        if ((int)threadIdx.x < G) { g.lo = ld_best_gpu(&recs[threadIdx.x].lo); g.hi = ld_best_gpu(&recs[threadIdx.x].hi); }
+        SVM_STAMP(11);
+        if ((int)threadIdx.x < G) rec_read<false>(recs + threadIdx.x, seq, g);
+        SVM_STAMP(12);
         best_warp_reduce(g);
         if (lane == 0) { sh.glo[warp] = g.lo; sh.ghi[warp] = g.hi; }
+        SVM_STAMP(13);
     }
     __syncthreads();
+    SVM_STAMP(14);
     best_init(mine);
-    for (int w = 0; w < gather_warps; ++w) best_merge(mine, sh.glo[w], sh.ghi[w]);
+    if (lane < gather_warps) { mine.lo = sh.glo[lane]; mine.hi = sh.ghi[lane]; }
+    best_warp_reduce(mine);
     SVM_STAMP(7);
 }
 
@@ -287,6 +348,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     uint64_t *bars = reinterpret_cast<uint64_t *>(slots + (size_t)WARPS * KS * row_bytes);
     Shared &sh = *reinterpret_cast<Shared *>(bars + WARPS * SMO_KSLOTS_MAX);
 
+
     // rows owned by this CTA and, inside it, by this warp (contiguous ranges)
     const long long n_own = a.row_end - a.row_begin;
     const long long r0 = a.row_begin + (long long)blockIdx.x * n_own / G;
@@ -296,6 +358,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     const long long w1 = r0 + (long long)(warp + 1) * R / WARPS;
     const int m = (int)(w1 - w0);
     const int keep_rows = (int)(((long long)m * a.keep_per_1024) >> 10);
+    const int ahead = (a.l2_ahead > 0 && m > a.kslots + a.l2_ahead) ? a.l2_ahead : 0;
 
     unsigned char *my_slots = slots + (size_t)warp * KS * row_bytes;
     uint64_t *my_bars = bars + warp * SMO_KSLOTS_MAX;
@@ -315,11 +378,20 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
             bulk_g2s(my_slots + (size_t)s * row_bytes, a.X + (size_t)(w0 + pf_row) * a.pitch4 * 4, (unsigned)row_bytes,
                      &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
+            if (ahead > 0) {             // and the row `ahead` places further on goes from HBM into L2
+                int r = pf_row + ahead;
+                if (r >= m) r -= m;
+                bulk_prefetch_l2(a.X + (size_t)(w0 + r) * a.pitch4 * 4, (unsigned)row_bytes, a.policy_stream);
+            }
         }
         if (++pf_row == m) pf_row = 0;
     };
-    if (m > 0)
+    if (m > 0) {
+        if (lane == 0)
+            for (int r = KS; r < KS + ahead; ++r)
+                bulk_prefetch_l2(a.X + (size_t)(w0 + r) * a.pitch4 * 4, (unsigned)row_bytes, a.policy_stream);
         for (int s = 0; s < KS; ++s) issue_into(s);
+    }
 
     // ---- exchange 0: selection over the initial state (main3.cpp:203-204 in the first iteration)
     LocalBest mine;
@@ -327,8 +399,6 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     for (long long j = r0 + threadIdx.x; j < r1; j += THREADS)
         best_consider(mine, j, a.f[j], a.alpha[j], a.y[j], a.cacheq ? a.cacheq[j] : -1, a.C, a.eps);
     int gather_no = 0;
-    exchange(a, sh, mine, gather_no);
-
     int num_iter = 1;                    // main3.cpp:197
     int stop = 0;
     double b_high = 0.0, b_low = 0.0;    // uninitialised in the reference (main3.cpp:188-189)
@@ -337,6 +407,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     long long x_passes = 0, cache_hits = 0;
 
     for (;;) {
+        exchange(a, sh, mine, gather_no);                                           // the one grid-wide synchronisation
+        if (num_iter > a.max_iter) { stop = 4; break; }                             // main3.cpp:283 (b keeps this iteration's b_high/b_low)
         const Best lo = mine.lo, hi = mine.hi;
         SVM_STAMP(0);
         SVM_GSTAMP(0);
@@ -368,13 +440,14 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 pv.h[i] = q < a.pitch4 ? __ldg(xh + q) : make_float4(0.f, 0.f, 0.f, 0.f);
                 pv.l[i] = q < a.pitch4 ? __ldg(xl + q) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
+            n_h = a.sqn[i_high];
+            n_l = a.sqn[i_low];
+            SVM_STAMP(15);
             double acc = 0.0;
 #pragma unroll
             for (int i = 0; i < Q; ++i)
                 if (i * 32 + lane < a.pitch4) accum_dot<CH>(pv.l[i], pv.h[i], acc);
             acc = warp_sum_butterfly(acc);
-            n_h = a.sqn[i_high];
-            n_l = a.sqn[i_low];
             K12 = svm_exp(-a.gamma * sqdist_from_dot(n_h, n_l, acc));
         } else {
             K12 = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low];
@@ -481,10 +554,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         SVM_GSTAMP(2);
         ++gather_no;
         mine = acc_best;
-        exchange(a, sh, mine, gather_no);
-
-        ++num_iter;                                              // main3.cpp:281-287
-        if (num_iter > a.max_iter) { stop = 4; break; }
+        ++num_iter;                                              // main3.cpp:281
     }
 
     // drain the ring: every requested copy must land before the CTA may exit

@@ -15,18 +15,24 @@ s = pkg.Solver(0)
 s.set_train_u8(X, y)
 o = s.smo_train(max_iter=k, cache_rows=cache)
 rows = min(k, 4000)
-t = np.zeros((rows, 8), dtype=np.int64)
+t = np.zeros((rows, 16), dtype=np.int64)
 assert s.L.svmb200_debug_timing(t.ctypes.data_as(C.c_void_p), rows) == 0
 t = t[20:rows - 1]                     # skip the cold start
 nxt = np.roll(t, -1, axis=0)[:-1]; t = t[:-1]
 ghz = 1.965
-seg = {"scalar (0->1)": t[:, 1] - t[:, 0], "pass (1->2)": t[:, 2] - t[:, 1], "warp reduce (2->3')": nxt[:, 3] - t[:, 2],
+seg = {"  pivot loads issued->arrived (0->15)": t[:, 15] - t[:, 0], "  K12+alpha math (15->1)": t[:, 1] - t[:, 15],
+       "  pub: smem read (4'->8')": nxt[:, 8] - nxt[:, 4], "  pub: warp reduce (8'->9')": nxt[:, 9] - nxt[:, 8],
+       "  pub: record stores (9'->10')": nxt[:, 10] - nxt[:, 9], "  pub: red (10'->5')": nxt[:, 5] - nxt[:, 10],
+       "  rd: barrier (6'->11')": nxt[:, 11] - nxt[:, 6], "  rd: record read (11'->12')": nxt[:, 12] - nxt[:, 11],
+       "  rd: warp reduce (12'->13')": nxt[:, 13] - nxt[:, 12], "  rd: barrier (13'->14')": nxt[:, 14] - nxt[:, 13],
+       "  rd: merge (14'->7')": nxt[:, 7] - nxt[:, 14],
+       "scalar (0->1)": t[:, 1] - t[:, 0], "pass (1->2)": t[:, 2] - t[:, 1], "warp reduce (2->3')": nxt[:, 3] - t[:, 2],
        "CTA barrier (3'->4')": nxt[:, 4] - nxt[:, 3], "CTA reduce+publish (4'->5')": nxt[:, 5] - nxt[:, 4], "spin on counter (5'->6')": nxt[:, 6] - nxt[:, 5],
        "read records+merge (6'->7')": nxt[:, 7] - nxt[:, 6], "to loop top (7'->0')": nxt[:, 0] - nxt[:, 7], "iteration (0->0')": nxt[:, 0] - t[:, 0]}
 print(f"n={n} iters={o['num_iter'] - 1} x_passes={o['x_passes']} cache_hits={o['cache_hits']} us/iter={1e3 * o['smo_ms'] / (o['num_iter'] - 1):.2f}")
 for name, v in seg.items():
     v = v[(v > 0) & (v < 10 ** 9)]
-    print(f"  {name:26s} median {np.median(v) / ghz / 1e3:7.3f} us   p90 {np.percentile(v, 90) / ghz / 1e3:7.3f} us")
+    print(f"  {name:38s} median {np.median(v) / ghz / 1e3:7.3f} us   p90 {np.percentile(v, 90) / ghz / 1e3:7.3f} us")
 # per-CTA globaltimer stamps of iterations 100..107: 0 loop top, 1 scalar done, 2 pass done
 if k > 110:
     G = o["grid_blocks"]
