@@ -141,6 +141,28 @@ int svmb200_select_pair(svmb200_ctx *ctx, const double *alpha, const double *f, 
 /* the scaled fp32 training matrix as stored in HBM (n x d, padding stripped) */
 int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs);
 
+/* ---- min/max for callers that cannot allocate (no counterpart in the reference) ----
+ * Per-feature minimum and maximum of a uint8 matrix that is ALREADY in device memory, written to
+ * device memory, for callers that must not allocate on the device: plugins running inside another
+ * framework's stream-ordered or pool-managed region, hosts whose allocator owns the whole GPU, loops
+ * that cannot afford the device-wide synchronisation an allocation may cause.  The reduction's
+ * scratch is a fixed 1 MiB table inside the library image (held by every GPU that loads the library,
+ * until the process exits), so this call performs no cudaMalloc / cudaFree and calls nothing that
+ * allocates.  Limits and rules:
+ *   - d <= SVMB200_NOALLOC_MAX_FEATURES, otherwise SVMB200_ELIMIT (message on stderr); n is unlimited;
+ *   - dev_X [n x d] row-major uint8, dev_min / dev_max [d] doubles: device pointers on `device`;
+ *   - the work is enqueued on `stream` (a cudaStream_t, NULL = default stream) and the call returns
+ *     without waiting: the results are ready when the stream reaches that point;
+ *   - the first call on each device looks up the table's address (one-time set-up): make that first
+ *     call before starting any stream capture on that device;
+ *   - all calls on one device share the table, so two calls whose kernels may overlap on the GPU
+ *     (different streams, no ordering between them) race; calls on one stream are safe.  The table
+ *     keeps the previous call's values, which is harmless: each call writes every entry it reads.
+ * Gives the same values as the min_out / max_out of svmb200_set_train_u8. */
+#define SVMB200_NOALLOC_MAX_FEATURES 1024
+int svmb200_minmax_u8_noalloc(int device, const uint8_t *dev_X, int64_t n, int32_t d, double *dev_min,
+                              double *dev_max, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

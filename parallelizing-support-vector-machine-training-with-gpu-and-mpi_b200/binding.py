@@ -82,6 +82,7 @@ def load_library():
     L.svmb200_kernel_row.argtypes = [vp, i64, dbl, i32, vp]
     L.svmb200_select_pair.argtypes = [vp, vp, vp, vp, i64, dbl, dbl, C.POINTER(i64), C.POINTER(i64)]
     L.svmb200_get_x_scaled.argtypes = [vp, vp]
+    L.svmb200_minmax_u8_noalloc.argtypes = [C.c_int, vp, i64, i32, vp, vp, vp]
     _lib = L
     return L
 
