@@ -42,6 +42,7 @@ extern "C" {
 #define SVMB200_STOP_INFEASIBLE  2  /* infeasible U and V                   main3.cpp:246 */
 #define SVMB200_STOP_ETA         3  /* non positive eta                     main3.cpp:253 */
 #define SVMB200_STOP_MAX_ITER    4  /* num_iter > max_iter                  main3.cpp:283 */
+#define SVMB200_STOP_PEER_LOST   5  /* row sharding only: a peer GPU's record never arrived (no counterpart) */
 
 typedef struct svmb200_ctx svmb200_ctx;
 
@@ -61,7 +62,7 @@ typedef struct {
                              rebuilt from it (mpi_svm_main2.cpp:167-183, "init = false"). */
     int32_t cache_rows;   /* HBM kernel-row cache capacity in rows; 0 = off (the reference's behaviour:
                              only the previous row is reused, main3.cpp:216-232); -1 = auto. */
-    int32_t accum_chunk;  /* fp32 squares summed before widening to FP64: 1, 2 or 4 (DESIGN.md
+    int32_t accum_chunk;  /* fp32 products summed before widening to FP64: 1, 2 or 4 (DESIGN.md
                              "Numerics"); 0 = library default. */
     int32_t trace_cap;    /* record the first trace_cap (i_high, i_low) pairs for svmb200_get_trace */
     int32_t l2_persist;   /* 0 = stream X with evict-first; 1 = keep a leading fraction of every
@@ -105,6 +106,13 @@ int svmb200_set_train_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y, 
  * (main3.cpp:347).  No statistics are computed; svmb200_predict_scaled_f64 is the matching call. */
 int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y, int64_t n, int32_t d);
 
+/* The same two steps on their own, for hosts that keep the reference's call sequence
+ * find_min_max(x, min, max, n, d); scale_features(x, min, max, n, d) on HOST vectors (main3.cpp:338-339,
+ * :355 for the test set): min/max of X [n x d], and in-place FP64 scaling (x - min) / range with
+ * range < 1e-12 -> 1.  Both run on the device in FP64 and return the reference's values bit for bit. */
+int svmb200_minmax_f64(svmb200_ctx *ctx, const double *X, int64_t n, int32_t d, double *min_out, double *max_out);
+int svmb200_scale_f64(svmb200_ctx *ctx, double *X_inout, const double *min_val, const double *max_val, int64_t n, int32_t d);
+
 /* ---- the solver: replaces SMO_train (main3.cpp:162-294; warm start mpi_svm_main2.cpp:154-288).
  * alpha: n doubles, written on return; read first when params->warm_start != 0.  b: (b_high+b_low)/2
  * (main3.cpp:291).  stats may be NULL. */
@@ -126,6 +134,22 @@ int svmb200_predict_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y_tes
                         int32_t ge_zero, int32_t *correct, double *scores);
 int svmb200_predict_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y_test, int64_t m,
                                int32_t ge_zero, int32_t *correct, double *scores);
+
+/* ---- row-sharded SMO over the GPUs of one box (BASELINE.json configs[3]; the reference scales N only
+ * through Cascade partitioning).  One process per GPU, each with its own context and the FULL training
+ * set uploaded (X is replicated so that both pivot rows are always local); GPU `rank` owns rows
+ * [n*rank/world, n*(rank+1)/world): their f, alpha, cache columns, and the X traffic of each iteration.
+ * Inside the persistent kernel every GPU stores one 128-byte record per iteration into every peer's
+ * mailbox over NVLink (peer-mapped memory) and reads the others' from its own -- no host, no NCCL on
+ * the path.  Set-up: every rank calls svmb200_shard_setup (gets a 64-byte CUDA IPC handle), the handles
+ * are all-gathered by the host (torch.distributed, MPI, ...), every rank calls svmb200_shard_connect
+ * with the `world` handles in rank order.  Afterwards all ranks call svmb200_smo_train in lockstep with
+ * the same parameters; on return b and stats are identical everywhere and alpha holds the rank's own
+ * rows (the others are 0 / untouched): all-gather alpha and install it with svmb200_set_model before
+ * svmb200_sv_ids / svmb200_predict_*.  Results are bit-identical to the single-GPU run. */
+int svmb200_shard_setup(svmb200_ctx *ctx, int32_t rank, int32_t world, void *handle_out /* 64 bytes */);
+int svmb200_shard_connect(svmb200_ctx *ctx, int32_t world, const void *handles /* world x 64 bytes */);
+int svmb200_set_model(svmb200_ctx *ctx, const double *alpha, double b);
 
 /* ---- introspection used by the parity tests ---- */
 /* (i_high, i_low) of the first min(cap, recorded) iterations that reached the update */

@@ -7,4 +7,4 @@ without the built library or without a B200 raises.
 """
 from .binding import (LIB_PATH, Params, Solver, Stats, SvmB200Error, STOP_NAMES, build_library,  # noqa: F401
                       declared_symbols, load_library)
-from . import datagen  # noqa: F401
+from . import binding, datagen  # noqa: F401

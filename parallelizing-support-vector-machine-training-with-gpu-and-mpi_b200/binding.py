@@ -12,7 +12,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG_DIR)
 LIB_PATH = os.path.join(PKG_DIR, "libsvmb200.so")
 HEADER = os.path.join(ROOT, "include", "svmb200.h")
-STOP_NAMES = {0: "converged", 1: "not_found", 2: "infeasible_uv", 3: "nonpositive_eta", 4: "max_iter"}
+STOP_NAMES = {0: "converged", 1: "not_found", 2: "infeasible_uv", 3: "nonpositive_eta", 4: "max_iter", 5: "peer_lost"}
 
 
 class SvmB200Error(RuntimeError):
@@ -73,6 +73,8 @@ def load_library():
     L.svmb200_set_train_u8.argtypes = [vp, vp, vp, i64, i32, vp, vp]
     L.svmb200_set_train_f64.argtypes = [vp, vp, vp, i64, i32, vp, vp]
     L.svmb200_set_train_scaled_f64.argtypes = [vp, vp, vp, i64, i32]
+    L.svmb200_minmax_f64.argtypes = [vp, vp, i64, i32, vp, vp]
+    L.svmb200_scale_f64.argtypes = [vp, vp, vp, vp, i64, i32]
     L.svmb200_smo_train.argtypes = [vp, C.POINTER(Params), vp, C.POINTER(dbl), C.POINTER(Stats)]
     L.svmb200_sv_ids.argtypes = [vp, vp, i32, C.POINTER(i32)]
     for name in ("svmb200_predict_u8", "svmb200_predict_f64", "svmb200_predict_scaled_f64"):
@@ -82,6 +84,9 @@ def load_library():
     L.svmb200_kernel_row.argtypes = [vp, i64, dbl, i32, vp]
     L.svmb200_select_pair.argtypes = [vp, vp, vp, vp, i64, dbl, dbl, C.POINTER(i64), C.POINTER(i64)]
     L.svmb200_get_x_scaled.argtypes = [vp, vp]
+    L.svmb200_shard_setup.argtypes = [vp, i32, i32, vp]
+    L.svmb200_shard_connect.argtypes = [vp, i32, vp]
+    L.svmb200_set_model.argtypes = [vp, vp, dbl]
     L.svmb200_minmax_u8_noalloc.argtypes = [C.c_int, vp, i64, i32, vp, vp, vp]
     _lib = L
     return L
@@ -153,6 +158,20 @@ class Solver:
         self._ck(self.L.svmb200_set_train_scaled_f64(self.h, _ptr(Xs), _ptr(y), n, d), "set_train_scaled_f64")
         self.n, self.d = n, d
 
+    def minmax_f64(self, X):
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        n, d = X.shape
+        mn, mx = np.zeros(d), np.zeros(d)
+        self._ck(self.L.svmb200_minmax_f64(self.h, _ptr(X), n, d, _ptr(mn), _ptr(mx)), "minmax_f64")
+        return mn, mx
+
+    def scale_f64(self, X, mn, mx):
+        X = np.ascontiguousarray(X, dtype=np.float64).copy()
+        n, d = X.shape
+        mn = np.ascontiguousarray(mn, dtype=np.float64); mx = np.ascontiguousarray(mx, dtype=np.float64)
+        self._ck(self.L.svmb200_scale_f64(self.h, _ptr(X), _ptr(mn), _ptr(mx), n, d), "scale_f64")
+        return X
+
     # ---- solver
     def smo_train(self, params: Params | None = None, alpha0=None, **kw):
         p = params or default_params(**kw)
@@ -192,6 +211,20 @@ class Solver:
 
     def predict_scaled(self, Xs, y_test=None, ge_zero=False):
         return self._predict(self.L.svmb200_predict_scaled_f64, Xs, np.float64, y_test, ge_zero)
+
+    # ---- row sharding over several GPUs (one process per GPU)
+    def shard_setup(self, rank: int, world: int) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._ck(self.L.svmb200_shard_setup(self.h, rank, world, buf), "shard_setup")
+        return buf.raw
+
+    def shard_connect(self, world: int, handles: bytes):
+        assert len(handles) == 64 * world
+        self._ck(self.L.svmb200_shard_connect(self.h, world, C.c_char_p(handles)), "shard_connect")
+
+    def set_model(self, alpha, b):
+        alpha = np.ascontiguousarray(alpha, dtype=np.float64)
+        self._ck(self.L.svmb200_set_model(self.h, _ptr(alpha), float(b)), "set_model")
 
     # ---- introspection
     def get_trace(self, cap):

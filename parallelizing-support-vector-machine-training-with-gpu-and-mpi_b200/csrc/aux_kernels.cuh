@@ -73,6 +73,19 @@ __global__ void scale_to_f32_kernel(const T *__restrict__ X, long long n, int d,
     }
 }
 
+// ---- FP64 in-place scaling for hosts that call scale_features on their own vectors (main3.cpp:74-89)
+__global__ void scale_f64_kernel(double *__restrict__ X, long long n, int d, const double *__restrict__ minv,
+                                 const double *__restrict__ maxv)
+{
+    const long long total = n * d;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+        const int col = (int)(g % d);
+        double range = maxv[col] - minv[col];
+        if (range < 1e-12) range = 1.0;
+        X[g] = (X[g] - minv[col]) / range;
+    }
+}
+
 // ---- squared norms |x_j|^2: the dot product of every row with itself, formed exactly as the solver
 // forms x_i . x_j (a warp per row), so that duplicates are at distance exactly 0
 template <int Q, int CH>

@@ -71,6 +71,11 @@ struct svmb200_ctx {
     double *svn = nullptr;
     int sv_alloc = 0;
 
+    // row sharding over several GPUs (one process per GPU; see svmb200_shard_*)
+    int shard_rank = 0, shard_world = 1, shard_epoch = 0;
+    Rec *mailbox = nullptr;              // [2][world], written by the peers over NVLink
+    Rec *peer_mailbox[8] = {};           // peer-mapped mailboxes ([rank] = mailbox)
+
     // generic scratch
     void *scratch = nullptr;
     size_t scratch_bytes = 0;
@@ -185,6 +190,9 @@ void svmb200_destroy(svmb200_ctx *ctx)
     cudaFree(ctx->X); cudaFree(ctx->y); cudaFree(ctx->sqn); cudaFree(ctx->svn); cudaFree(ctx->minv); cudaFree(ctx->maxv);
     cudaFree(ctx->f); cudaFree(ctx->alpha); cudaFree(ctx->cacheq); cudaFree(ctx->cacheK);
     cudaFree(ctx->rec); cudaFree(ctx->result); cudaFree(ctx->trace);
+    for (int p = 0; p < ctx->shard_world; ++p)
+        if (p != ctx->shard_rank && ctx->peer_mailbox[p]) cudaIpcCloseMemHandle(ctx->peer_mailbox[p]);
+    cudaFree(ctx->mailbox);
     cudaFree(ctx->svX); cudaFree(ctx->svcoef); cudaFree(ctx->scratch);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev2);
     cudaStreamDestroy(ctx->stream);
@@ -288,6 +296,48 @@ int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32
 }
 
 } // extern "C"
+
+extern "C" int svmb200_minmax_f64(svmb200_ctx *ctx, const double *X, int64_t n, int32_t d, double *min_out, double *max_out)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!X || !min_out || !max_out || n <= 0 || d <= 0) FAIL(SVMB200_EINVAL, "bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    const int parts = (int)std::min<long long>(ctx->num_sms * 4, (n + 63) / 64);
+    const size_t stat_bytes = ((size_t)(2 * parts + 2) * d * sizeof(double) + 255) & ~(size_t)255;
+    if (int rc = ensure_scratch(ctx, stat_bytes + (size_t)n * d * sizeof(double))) return rc;
+    double *pmin = static_cast<double *>(ctx->scratch), *pmax = pmin + (size_t)parts * d, *mn = pmax + (size_t)parts * d, *mx = mn + d;
+    double *raw = reinterpret_cast<double *>(static_cast<char *>(ctx->scratch) + stat_bytes);
+    CK(cudaMemcpyAsync(raw, X, (size_t)n * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    colminmax_partial_kernel<double><<<parts, 256, 0, ctx->stream>>>(raw, n, d, (int)((n + parts - 1) / parts), pmin, pmax);
+    colminmax_final_kernel<<<(d + 127) / 128, 128, 0, ctx->stream>>>(pmin, pmax, parts, d, mn, mx);
+    ctx->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(min_out, mn, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(max_out, mx, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SVMB200_OK;
+}
+
+extern "C" int svmb200_scale_f64(svmb200_ctx *ctx, double *X, const double *min_val, const double *max_val, int64_t n, int32_t d)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!X || !min_val || !max_val || n <= 0 || d <= 0) FAIL(SVMB200_EINVAL, "bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    const size_t stat_bytes = ((size_t)2 * d * sizeof(double) + 255) & ~(size_t)255;
+    if (int rc = ensure_scratch(ctx, stat_bytes + (size_t)n * d * sizeof(double))) return rc;
+    double *mn = static_cast<double *>(ctx->scratch), *mx = mn + d;
+    double *raw = reinterpret_cast<double *>(static_cast<char *>(ctx->scratch) + stat_bytes);
+    CK(cudaMemcpyAsync(mn, min_val, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(mx, max_val, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(raw, X, (size_t)n * d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    const long long total = (long long)n * d;
+    scale_f64_kernel<<<(int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(raw, n, d, mn, mx);
+    ctx->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(X, raw, (size_t)n * d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SVMB200_OK;
+}
 
 // ------------------------------------------------------------------------------------------
 static int q_for_pitch(int pitch4)
@@ -492,7 +542,8 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps) > (size_t)ctx->max_smem_optin) --kslots;
     const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
-    const int grid = (int)std::max<long long>(1, std::min<long long>(ctx->num_sms, (n + 7) / 8));
+    const long long n_own = n * (ctx->shard_rank + 1) / ctx->shard_world - n * ctx->shard_rank / ctx->shard_world;
+    const int grid = (int)std::max<long long>(1, std::min<long long>(ctx->num_sms, (n_own + 7) / 8));
 
     // row cache
     int cache_cap = params->cache_rows;
@@ -565,7 +616,12 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
     a.l2_ahead = 0;
     if (const char *e = getenv("SVMB200_L2AHEAD")) a.l2_ahead = std::max(0, std::min(32, atoi(e)));
-    a.peers = 1; a.rank = 0; a.row_begin = 0; a.row_end = n; a.mailbox = nullptr;
+    a.peers = ctx->shard_world; a.rank = ctx->shard_rank;
+    a.row_begin = n * ctx->shard_rank / ctx->shard_world;
+    a.row_end = n * (ctx->shard_rank + 1) / ctx->shard_world;
+    a.mailbox = ctx->mailbox;
+    for (int p = 0; p < 8; ++p) a.peer_mailbox[p] = ctx->peer_mailbox[p];
+    a.epoch = ++ctx->shard_epoch;
     a.timing = nullptr; a.timing_cap = 0;
 #ifdef SVM_TIMING
     {
@@ -617,6 +673,61 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         stats->grid_blocks = grid;
         stats->launches = ctx->launches - launches0;
     }
+    return SVMB200_OK;
+}
+
+// ---- row sharding across GPUs: one process per GPU, X replicated, rows [n*rank/world, n*(rank+1)/world) owned
+extern "C" int svmb200_shard_setup(svmb200_ctx *ctx, int32_t rank, int32_t world, void *handle_out)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (world < 1 || world > 8 || rank < 0 || rank >= world || !handle_out) FAIL(SVMB200_EINVAL, "rank/world out of range (world <= 8)");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->mailbox) FAIL(SVMB200_ESTATE, "svmb200_shard_setup called twice");
+    CK(cudaMalloc(&ctx->mailbox, (size_t)2 * 8 * sizeof(Rec)));
+    CK(cudaMemset(ctx->mailbox, 0, (size_t)2 * 8 * sizeof(Rec)));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, ctx->mailbox));
+    memcpy(handle_out, &h, sizeof h);
+    ctx->shard_rank = rank;
+    ctx->shard_world = 1;          // becomes `world` in svmb200_shard_connect
+    ctx->peer_mailbox[rank] = ctx->mailbox;
+    return SVMB200_OK;
+}
+
+extern "C" int svmb200_shard_connect(svmb200_ctx *ctx, int32_t world, const void *handles)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!ctx->mailbox) FAIL(SVMB200_ESTATE, "svmb200_shard_connect before svmb200_shard_setup");
+    if (world < 1 || world > 8 || ctx->shard_rank >= world || !handles) FAIL(SVMB200_EINVAL, "bad world / handles");
+    CK(cudaSetDevice(ctx->device));
+    for (int p = 0; p < world; ++p) {
+        if (p == ctx->shard_rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, static_cast<const char *>(handles) + (size_t)p * 64, 64);
+        void *ptr = nullptr;
+        CK(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+        ctx->peer_mailbox[p] = static_cast<Rec *>(ptr);
+    }
+    ctx->shard_world = world;
+    ctx->shard_epoch = 0;
+    return SVMB200_OK;
+}
+
+// install a model (alpha of all rows, b) -- used after a sharded run, when every GPU holds only its rows' alpha
+extern "C" int svmb200_set_model(svmb200_ctx *ctx, const double *alpha, double b)
+{
+    if (!ctx || !alpha) return SVMB200_EINVAL;
+    if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set");
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->trained) { svmb200_default_params(&ctx->params); ctx->params.accum_chunk = DEFAULT_CHUNK; }
+    ctx->alpha_host.assign(alpha, alpha + ctx->n);
+    ctx->b = b;
+    ctx->sv_ids.clear();
+    for (long long i = 0; i < ctx->n; ++i)
+        if (alpha[i] > ctx->params.sv_tol) ctx->sv_ids.push_back((int)i);
+    CK(cudaMemcpy(ctx->alpha, alpha, (size_t)ctx->n * sizeof(double), cudaMemcpyHostToDevice));
+    ctx->trained = true;
     return SVMB200_OK;
 }
 

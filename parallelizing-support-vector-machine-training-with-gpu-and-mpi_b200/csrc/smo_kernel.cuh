@@ -70,7 +70,8 @@ struct SmoArgs {
     int rank;                           // this GPU
     long long row_begin, row_end;       // rows owned by this GPU (X is replicated, state is global-sized)
     Rec *mailbox;                       // [2][peers] local mailbox written by peers
-    Rec *peer_mailbox[8];               // peers' mailboxes (peer-mapped device pointers)
+    Rec *peer_mailbox[8];               // peers' mailboxes (peer-mapped device pointers; [rank] is the local one)
+    int epoch;                          // launch number, folded into the mailbox words so that stale records never match
     long long *timing;                  // optional [iterations][8] clock64 stamps of CTA 0 (profiling builds only)
     int timing_cap;
 };
@@ -238,9 +239,10 @@ __device__ __forceinline__ void rec_store(Rec *r, const LocalBest &b, unsigned s
         else asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
     }
 }
-// read a record; re-read until all 16 words carry `seq`
+// read a record; re-read until all 16 words carry `seq`.  Returns false when `budget` polls pass
+// without that (only the multi-GPU mailbox reads pass a finite budget: a peer process may have died).
 template <bool SYS>
-__device__ __forceinline__ void rec_read(const Rec *r, unsigned seq, LocalBest &out)
+__device__ __forceinline__ bool rec_read(const Rec *r, unsigned seq, LocalBest &out, long long deadline_clock = 0)
 {
     unsigned long long w[REC_WORDS];
     for (;;) {
@@ -253,8 +255,10 @@ __device__ __forceinline__ void rec_read(const Rec *r, unsigned seq, LocalBest &
 #pragma unroll
         for (int k = 0; k < REC_WORDS; ++k) ok = ok && ((unsigned)(w[k] >> 32) == seq);
         if (ok) break;
+        if (deadline_clock && clock64() > deadline_clock) return false;
     }
     rec_unpack(w, out);
+    return true;
 }
 __device__ __forceinline__ void red_relaxed_gpu_add(unsigned *p, unsigned v)
 {
@@ -281,9 +285,14 @@ __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; a
 #define SVM_GSTAMP(k) do { } while (0)
 #endif
 
-// One exchange: CTA-level reduce of the per-thread candidates, publish, gather.  On return every
-// thread of every CTA holds the same grid-wide winners in `mine`.
-__device__ __forceinline__ void exchange(const SmoArgs &a, Shared &sh, LocalBest &mine, int gather_no)
+constexpr long long PEER_TIMEOUT_CLOCKS = 6000000000LL;   // ~3 s at 1.97 GHz: a peer GPU's process is gone
+
+// One exchange: CTA-level reduce of the per-thread candidates, publish, gather; with row sharding over
+// several GPUs a second level follows in which every GPU stores its record into every peer's mailbox
+// over NVLink (peer-mapped memory, same self-validating words) and reads the others' from its own.
+// On return every thread of every CTA on every GPU holds the same winners in `mine`.  Returns false
+// if a peer never showed up.
+__device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest &mine, int gather_no)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x;
@@ -331,6 +340,28 @@ __device__ __forceinline__ void exchange(const SmoArgs &a, Shared &sh, LocalBest
     if (lane < gather_warps) { mine.lo = sh.glo[lane]; mine.hi = sh.ghi[lane]; }
     best_warp_reduce(mine);
     SVM_STAMP(7);
+    if (a.peers == 1) return true;
+
+    // ---- second level: one record per GPU, all-gathered through the peers' mailboxes
+    const unsigned seq2 = ((unsigned)(a.epoch & 0x7ff) << 21) | seq;
+    const int slot = (gather_no & 1) * a.peers;
+    if (blockIdx.x == 0 && threadIdx.x < a.peers)        // thread p stores this GPU's record at peer p (p == rank: local)
+        rec_store<true>(a.peer_mailbox[threadIdx.x] + slot + a.rank, mine, seq2);
+    bool ok = true;
+    if (warp == 0) {
+        LocalBest g;
+        best_init(g);
+        if (lane < a.peers) ok = rec_read<true>(a.mailbox + slot + lane, seq2, g, clock64() + PEER_TIMEOUT_CLOCKS);
+        ok = __all_sync(FULL, ok);
+        best_warp_reduce(g);
+        if (lane == 0) { sh.glo[0] = g.lo; sh.ghi[0] = g.hi; sh.glo[1].idx = ok ? 1 : 0; }
+    }
+    __syncthreads();
+    mine.lo = sh.glo[0];
+    mine.hi = sh.ghi[0];
+    ok = sh.glo[1].idx != 0;
+    __syncthreads();                                      // glo[0..1] are rewritten by the next exchange
+    return ok;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -407,7 +438,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     long long x_passes = 0, cache_hits = 0;
 
     for (;;) {
-        exchange(a, sh, mine, gather_no);                                           // the one grid-wide synchronisation
+        if (!exchange(a, sh, mine, gather_no)) { stop = 5; break; }                 // the one grid-wide synchronisation
         if (num_iter > a.max_iter) { stop = 4; break; }                             // main3.cpp:283 (b keeps this iteration's b_high/b_low)
         const Best lo = mine.lo, hi = mine.hi;
         SVM_STAMP(0);
@@ -449,8 +480,21 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 if (i * 32 + lane < a.pitch4) accum_dot<CH>(pv.l[i], pv.h[i], acc);
             acc = warp_sum_butterfly(acc);
             K12 = svm_exp(-a.gamma * sqdist_from_dot(n_h, n_l, acc));
-        } else {
+        } else if (i_low >= a.row_begin && i_low < a.row_end) {
             K12 = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low];
+        } else {
+            // row sharding: column i_low of the cached rows lives on the GPU that owns row i_low; X is
+            // replicated, so form K12 here the way that GPU formed it (same code, same bits)
+            const float4 *xh = reinterpret_cast<const float4 *>(a.X) + (size_t)i_high * a.pitch4;
+            const float4 *xl = reinterpret_cast<const float4 *>(a.X) + (size_t)i_low * a.pitch4;
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i < Q; ++i) {
+                const int q = i * 32 + lane;
+                if (q < a.pitch4) accum_dot<CH>(__ldg(xl + q), __ldg(xh + q), acc);
+            }
+            acc = warp_sum_butterfly(acc);
+            K12 = svm_exp(-a.gamma * sqdist_from_dot(a.sqn[i_high], a.sqn[i_low], acc));
         }
 
         // scalar update, main3.cpp:235-270, operation for operation

@@ -1,0 +1,92 @@
+"""Cascade SVM (star: code/mpi_svm_main2.cpp, tree: code/mpi_svm_main3.cpp) -- world_size 2 and 4 over gloo.
+
+The oracle here is the reference itself: the UNMODIFIED mpi_svm_main2/3.cpp compiled against the fork/pipe MPI
+shim (oracle/mpi_shim/mpi.h -> oracle/_ref/mpi_svm2, mpi_svm3) and run on the same synthetic CSVs.  With the CPU
+checker as the per-rank solver the merge protocol of parallel.py must reproduce the reference's printed result
+exactly (b to its 15 printed digits, SV count, rounds, accuracy); with the GPU solver (-m gpu) the SV-ID set and
+accuracy must be those of the CPU run and b within 1e-4."""
+import json
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = {"star": os.path.join(ROOT, "oracle", "_ref", "mpi_svm2"), "tree": os.path.join(ROOT, "oracle", "_ref", "mpi_svm3")}
+N, M = 1200, 300
+_ref_cache = {}
+
+
+def _reference(mode, world, pkg, tmp_path_factory):
+    key = (mode, world)
+    if key in _ref_cache:
+        return _ref_cache[key]
+    if not os.path.exists(REF[mode]):
+        pytest.skip("oracle/_ref cascade binaries not built")
+    d = tmp_path_factory.mktemp(f"ref_{mode}_{world}")
+    X, dg = pkg.datagen.make_dataset(N)
+    Xt, dgt = pkg.datagen.make_dataset(M, split=1)
+    pkg.datagen.write_csv(str(d / "mnist3_train_data.csv"), X, dg)        # the names the reference hard-codes (mpi_svm_main2.cpp:316-321)
+    pkg.datagen.write_csv(str(d / "mnist3_test_data.csv"), Xt, dgt)
+    out = subprocess.run([REF[mode]], cwd=d, env=dict(os.environ, MPI_SHIM_NP=str(world)), capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr
+    t = out.stdout
+    res = {"b": re.search(r"Final b = ([-0-9.]+)", t).group(1),
+           "sv_count": int(re.search(r"Converged at round \d+, SV count = (\d+)", t).group(1)),
+           "rounds": int(re.search(r"Cascade finished in (\d+) rounds", t).group(1)),
+           "correct": int(re.search(r"\((\d+)/%d\)" % M, t).group(1))}
+    _ref_cache[key] = res
+    return res
+
+
+def _run_ours(mode, world, solver, tmp_path):
+    out = tmp_path / f"{mode}_{world}_{solver}.json"
+    port = 29500 + (os.getpid() + hash((mode, world, solver))) % 2000
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "cascade_worker.py"), mode, str(N), str(M), str(out), solver]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=dict(os.environ, OMP_NUM_THREADS="1"))
+    assert r.returncode == 0, r.stderr[-3000:]
+    return json.load(open(out))
+
+
+@pytest.mark.parametrize("mode,world", [("star", 2), ("tree", 2), ("star", 4), ("tree", 4)])
+def test_cascade_protocol_matches_reference(mode, world, pkg, tmp_path, tmp_path_factory):
+    ref = _reference(mode, world, pkg, tmp_path_factory)
+    ours = _run_ours(mode, world, "oracle", tmp_path)
+    assert ours["converged"]
+    assert f"{ours['b']:.15f}" == ref["b"]
+    assert len(ours["sv_ids"]) == ref["sv_count"]
+    assert ours["rounds"] == ref["rounds"]
+    assert ours["correct"] == ref["correct"]
+
+
+def test_tree_rejects_non_power_of_two(pkg):
+    from svmb200 import parallel
+    import torch.distributed as dist
+    # world is checked before any collective: emulate with a 3-rank view
+    class Fake:
+        pass
+    orig = (dist.get_rank, dist.get_world_size)
+    dist.get_rank, dist.get_world_size = (lambda: 0), (lambda: 3)
+    try:
+        with pytest.raises(ValueError, match="power of two"):      # mpi_svm_main3.cpp:420-428
+            parallel.cascade_tree(None, None, None, None)
+    finally:
+        dist.get_rank, dist.get_world_size = orig
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["star", "tree"])
+def test_cascade_on_gpu_matches_reference(mode, pkg, tmp_path, tmp_path_factory):
+    """Two ranks, both on cuda:0 (their kernels never wait on each other), collectives over gloo."""
+    ours = _run_ours(mode, 2, "gpu", tmp_path)
+    cpu = _run_ours(mode, 2, "oracle", tmp_path)
+    assert ours["converged"]
+    assert ours["sv_ids"] == cpu["sv_ids"]
+    assert abs(ours["b"] - cpu["b"]) <= 1e-4 * max(1.0, abs(cpu["b"]))
+    assert ours["correct"] == cpu["correct"]
+    if os.path.exists(REF[mode]):
+        ref = _reference(mode, 2, pkg, tmp_path_factory)
+        assert len(ours["sv_ids"]) == ref["sv_count"] and ours["correct"] == ref["correct"]

@@ -41,6 +41,10 @@ def test_preprocessing_matches_oracle(solver, O, dataset):
     assert np.array_equal(solver.get_x_scaled(), xs.astype(np.float32))
     solver.set_train_scaled(xs, y)
     assert np.array_equal(solver.get_x_scaled(), xs.astype(np.float32))
+    # the host-vector forms of find_min_max / scale_features: FP64 in, FP64 out, the reference's bits
+    mn3, mx3 = solver.minmax_f64(X.astype(np.float64))
+    assert np.array_equal(mn3, mno) and np.array_equal(mx3, mxo)
+    assert np.array_equal(solver.scale_f64(X.astype(np.float64), mn3, mx3), xs)
 
 
 @pytest.mark.parametrize("chunk", [1, 2, 4])
