@@ -1,3 +1,1 @@
-timeout 200 python -m pytest tests -m gpu -x -q --tb=short --timeout 60 2>&1 | tail -5
-echo "--- alone, fresh process"
-timeout 100 python -m pytest tests/test_zz_no_alloc.py -m gpu -q --tb=short --timeout 60 2>&1 | tail -5
+timeout 400 python -m pytest tests -m gpu -x -q --tb=short --timeout 200 2>&1 | tail -8

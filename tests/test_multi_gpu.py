@@ -1,0 +1,35 @@
+"""Row-sharded SMO across GPUs (needs >= 2 GPUs: `gpurun --gpus 2`; skipped on a 1-GPU box)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_row_sharded_smo_is_bit_identical_to_one_gpu(world, tmp_path):
+    if _ngpu() < world:
+        pytest.skip(f"needs {world} GPUs")
+    out = tmp_path / "mgpu.json"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29400 + world), os.path.join(ROOT, "tests", "mgpu_worker.py"), "3000", str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    allres = json.load(open(out))
+    assert len(allres) == world
+    for res in allres:
+        for label in ("cache_off", "cache_on", "cache_small"):
+            v = res[label]
+            assert v["stop"] == 0 and v["iters"] == v["ref_iters"], (label, v)
+            assert v["alpha_equal"] and v["b_equal"] and v["trace_equal"] and v["sv_equal"], (label, v)
+        assert res["cache_on"]["cache_hits"] > 0 and res["cache_off"]["cache_hits"] == 0
+    assert len({r["correct"] for r in allres}) == 1
