@@ -274,6 +274,8 @@ __device__ __forceinline__ unsigned ld_relaxed_gpu_u32(const unsigned *p)
 struct __align__(16) Shared {
     Best wlo[SMO_MAX_WARPS], whi[SMO_MAX_WARPS];  // per-warp winners of this CTA's rows
     Best glo[SMO_MAX_WARPS], ghi[SMO_MAX_WARPS];  // per-warp winners over the gathered records
+    Best xlo, xhi;                                // winners over the GPUs' records (row sharding)
+    int xok, xpad_[3];
 };
 
 #ifdef SVM_TIMING
@@ -318,6 +320,7 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
             SVM_STAMP(5);
             const unsigned target = (unsigned)G * seq;
             while ((int)(ld_relaxed_gpu_u32(a.arrive) - target) < 0) { }
+            __threadfence();      // orders the cached-row reads after the arrivals observed here (pairs with the writers' fence)
             SVM_STAMP(6);
         }
     }
@@ -354,14 +357,13 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
         if (lane < a.peers) ok = rec_read<true>(a.mailbox + slot + lane, seq2, g, clock64() + PEER_TIMEOUT_CLOCKS);
         ok = __all_sync(FULL, ok);
         best_warp_reduce(g);
-        if (lane == 0) { sh.glo[0] = g.lo; sh.ghi[0] = g.hi; sh.glo[1].idx = ok ? 1 : 0; }
+        if (lane == 0) { sh.xlo = g.lo; sh.xhi = g.hi; sh.xok = ok ? 1 : 0; }
     }
     __syncthreads();
-    mine.lo = sh.glo[0];
-    mine.hi = sh.ghi[0];
-    ok = sh.glo[1].idx != 0;
-    __syncthreads();                                      // glo[0..1] are rewritten by the next exchange
-    return ok;
+    mine.lo = sh.xlo;
+    mine.hi = sh.xhi;
+    ok = sh.xok != 0;
+    return ok;                                            // xlo/xhi/xok are next written two CTA barriers from here
 }
 
 // ------------------------------------------------------------------------------------------
@@ -481,7 +483,10 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             acc = warp_sum_butterfly(acc);
             K12 = svm_exp(-a.gamma * sqdist_from_dot(n_h, n_l, acc));
         } else if (i_low >= a.row_begin && i_low < a.row_end) {
-            K12 = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low];
+            // the one read of a value another CTA wrote: column i_low of the cached row was stored by the CTA that
+            // owns row i_low, at least one exchange ago (its __threadfence below, this CTA's fence after the counter
+            // spin).  Read it from L2: this SM's L1 may still hold the line from when the slot cached another row.
+            K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
         } else {
             // row sharding: column i_low of the cached rows lives on the GPU that owns row i_low; X is
             // replicated, so form K12 here the way that GPU formed it (same code, same bits)
@@ -572,6 +577,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     a.f[j] = fj;
                     if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
                     if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
+                    if (slot_h >= 0 && !(hit_h && hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
                     if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
                     if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
                     best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);

@@ -144,6 +144,14 @@ def test_cache_on_equals_cache_off(solver, O, dataset):
         if cap == -1:
             assert on["cache_hits"] > 0.5 * on["num_iter"]
     assert off["cache_hits"] == 0 and off["x_passes"] == off["num_iter"] - 1
+    # few rows per CTA and a cache far smaller than the working set: slots are recycled every few iterations, so a
+    # K12 read from a recycled slot must not come from a stale L1 line of another SM
+    X, _, y = dataset(300)
+    solver.set_train_u8(X, y)
+    off = solver.smo_train(cache_rows=0)
+    for cap in (3, 8, 32):
+        on = solver.smo_train(cache_rows=cap)
+        assert np.array_equal(on["alpha"], off["alpha"]) and on["b"] == off["b"] and on["num_iter"] == off["num_iter"], cap
 
 
 def test_warm_start_matches_oracle(solver, O, dataset):

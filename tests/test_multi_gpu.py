@@ -25,6 +25,7 @@ def test_row_sharded_smo_is_bit_identical_to_one_gpu(world, tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-3000:]
     allres = json.load(open(out))
+    print(json.dumps(allres[0]))
     assert len(allres) == world
     for res in allres:
         for label in ("cache_off", "cache_on", "cache_small"):
