@@ -135,6 +135,13 @@ int svmb200_predict_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y_tes
 int svmb200_predict_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y_test, int64_t m,
                                int32_t ge_zero, int32_t *correct, double *scores);
 
+/* ---- model persistence: the dump the reference left commented out (mpi_svm_main2.cpp:686-697: SV ids,
+ * labels, alphas, b) as one binary file that also holds the scaled SV rows and the train statistics.
+ * svmb200_load_model turns the context into a predict-only one (its training set, if any, is dropped):
+ * svmb200_predict_* and svmb200_sv_ids work, svmb200_smo_train needs a new svmb200_set_train_*. */
+int svmb200_save_model(svmb200_ctx *ctx, const char *path);
+int svmb200_load_model(svmb200_ctx *ctx, const char *path);
+
 /* ---- row-sharded SMO over the GPUs of one box (BASELINE.json configs[3]; the reference scales N only
  * through Cascade partitioning).  One process per GPU, each with its own context and the FULL training
  * set uploaded (X is replicated so that both pivot rows are always local); GPU `rank` owns rows

@@ -84,6 +84,8 @@ def load_library():
     L.svmb200_kernel_row.argtypes = [vp, i64, dbl, i32, vp]
     L.svmb200_select_pair.argtypes = [vp, vp, vp, vp, i64, dbl, dbl, C.POINTER(i64), C.POINTER(i64)]
     L.svmb200_get_x_scaled.argtypes = [vp, vp]
+    L.svmb200_save_model.argtypes = [vp, C.c_char_p]
+    L.svmb200_load_model.argtypes = [vp, C.c_char_p]
     L.svmb200_shard_setup.argtypes = [vp, i32, i32, vp]
     L.svmb200_shard_connect.argtypes = [vp, i32, vp]
     L.svmb200_set_model.argtypes = [vp, vp, dbl]
@@ -211,6 +213,12 @@ class Solver:
 
     def predict_scaled(self, Xs, y_test=None, ge_zero=False):
         return self._predict(self.L.svmb200_predict_scaled_f64, Xs, np.float64, y_test, ge_zero)
+
+    def save_model(self, path: str):
+        self._ck(self.L.svmb200_save_model(self.h, path.encode()), "save_model")
+
+    def load_model(self, path: str):
+        self._ck(self.L.svmb200_load_model(self.h, path.encode()), "load_model")
 
     # ---- row sharding over several GPUs (one process per GPU)
     def shard_setup(self, rank: int, world: int) -> bytes:

@@ -69,6 +69,9 @@ struct svmb200_ctx {
     float *svX = nullptr;
     double *svcoef = nullptr;
     double *svn = nullptr;
+    bool model_ready = false;   // svX / svcoef / svn hold the support vectors of the current model
+    int model_nsv = 0;
+    std::vector<int> model_y;   // labels of the support vectors (kept for svmb200_save_model)
     int sv_alloc = 0;
 
     // row sharding over several GPUs (one process per GPU; see svmb200_shard_*)
@@ -229,6 +232,7 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
     ctx->trained = false;
     ctx->have_stats = false;
     ctx->sqn_chunk = 0;
+    ctx->model_ready = false;
     return 0;
 }
 
@@ -584,6 +588,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         for (long long j = 0; j < n; ++j)
             if (alpha[j] != 0.0) { nz.push_back((int)j); nzy.push_back(y_host[j]); }
         if (int rc = build_sv_block(ctx, nz, alpha, nzy)) return rc;
+        ctx->model_ready = false;
         init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 0, 0);
         ctx->launches += 1;
         CK(cudaGetLastError());
@@ -608,14 +613,17 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     {
         // L2 residency: when X does not fit in L2, keep a leading share of every warp's rows
         const double x_bytes = (double)n * ctx->pitch4 * 16;
-        const double l2_keep_budget = 96.0 * 1024 * 1024;
+        double l2_keep_budget = 96.0 * 1024 * 1024;
+        if (const char *e = getenv("SVMB200_L2KEEP_MB")) l2_keep_budget = atof(e) * 1024 * 1024;
         int persist = params->l2_persist;
         if (persist < 0) persist = 1;
-        if (x_bytes <= l2_keep_budget) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
+        if (x_bytes <= 96.0 * 1024 * 1024) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
         else if (persist) a.keep_per_1024 = (int)(1024.0 * l2_keep_budget / x_bytes);
     }
     a.l2_ahead = 0;
     if (const char *e = getenv("SVMB200_L2AHEAD")) a.l2_ahead = std::max(0, std::min(32, atoi(e)));
+    a.l2_burst = 0;
+    if (const char *e = getenv("SVMB200_L2BURST")) a.l2_burst = std::max(0, std::min(16, atoi(e)));
     a.peers = ctx->shard_world; a.rank = ctx->shard_rank;
     a.row_begin = n * ctx->shard_rank / ctx->shard_world;
     a.row_end = n * (ctx->shard_rank + 1) / ctx->shard_world;
@@ -653,6 +661,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         if (alpha[i] > params->sv_tol) ctx->sv_ids.push_back((int)i);
     ctx->trace_count = std::min(trace_cap, r.num_iter - 1);
     ctx->trained = true;
+    ctx->model_ready = false;
 
     if (stats) {
         float ms_init = 0.f, ms_smo = 0.f;
@@ -728,6 +737,109 @@ extern "C" int svmb200_set_model(svmb200_ctx *ctx, const double *alpha, double b
         if (alpha[i] > ctx->params.sv_tol) ctx->sv_ids.push_back((int)i);
     CK(cudaMemcpy(ctx->alpha, alpha, (size_t)ctx->n * sizeof(double), cudaMemcpyHostToDevice));
     ctx->trained = true;
+    ctx->model_ready = false;
+    return SVMB200_OK;
+}
+
+static int ensure_model(svmb200_ctx *ctx);
+
+// ---- model persistence: the dump the reference left commented out (mpi_svm_main2.cpp:686-697: SV ids, labels,
+// alphas, b), as one binary file that also carries the scaled SV rows and the scaling statistics, so that a
+// predict-only process needs no training set.
+namespace {
+struct ModelHeader {
+    char magic[8];          // "SVMB200M"
+    uint32_t version;
+    int32_t d, pitch4, n_sv, accum_chunk, have_stats;
+    double gamma, b, sv_tol;
+};
+}
+
+extern "C" int svmb200_save_model(svmb200_ctx *ctx, const char *path)
+{
+    if (!ctx || !path) return SVMB200_EINVAL;
+    if (!ctx->trained) FAIL(SVMB200_ESTATE, "no model to save");
+    CK(cudaSetDevice(ctx->device));
+    if (int rc = ensure_model(ctx)) return rc;
+    const int nsv = ctx->model_nsv;
+    ModelHeader h{};
+    memcpy(h.magic, "SVMB200M", 8);
+    h.version = 1; h.d = ctx->d; h.pitch4 = ctx->pitch4; h.n_sv = nsv; h.accum_chunk = ctx->params.accum_chunk;
+    h.have_stats = ctx->have_stats ? 1 : 0; h.gamma = ctx->params.gamma; h.b = ctx->b; h.sv_tol = ctx->params.sv_tol;
+    std::vector<double> mn(ctx->d), mx(ctx->d), al(nsv);
+    std::vector<float> rows((size_t)nsv * ctx->pitch4 * 4);
+    if (ctx->have_stats) {
+        CK(cudaMemcpy(mn.data(), ctx->minv, (size_t)ctx->d * sizeof(double), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(mx.data(), ctx->maxv, (size_t)ctx->d * sizeof(double), cudaMemcpyDeviceToHost));
+    }
+    if (nsv) CK(cudaMemcpy(rows.data(), ctx->svX, rows.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < nsv; ++k) al[k] = ctx->alpha_host[ctx->sv_ids[k]];
+    FILE *f = fopen(path, "wb");
+    if (!f) FAIL(SVMB200_EINVAL, "cannot open %s for writing", path);
+    bool ok = fwrite(&h, sizeof h, 1, f) == 1;
+    if (ctx->have_stats) ok = ok && fwrite(mn.data(), sizeof(double), ctx->d, f) == (size_t)ctx->d && fwrite(mx.data(), sizeof(double), ctx->d, f) == (size_t)ctx->d;
+    ok = ok && fwrite(ctx->sv_ids.data(), sizeof(int), nsv, f) == (size_t)nsv && fwrite(ctx->model_y.data(), sizeof(int), nsv, f) == (size_t)nsv &&
+         fwrite(al.data(), sizeof(double), nsv, f) == (size_t)nsv && fwrite(rows.data(), sizeof(float), rows.size(), f) == rows.size();
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) FAIL(SVMB200_EINVAL, "short write to %s", path);
+    return SVMB200_OK;
+}
+
+extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
+{
+    if (!ctx || !path) return SVMB200_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    FILE *f = fopen(path, "rb");
+    if (!f) FAIL(SVMB200_EINVAL, "cannot open %s", path);
+    ModelHeader h{};
+    bool ok = fread(&h, sizeof h, 1, f) == 1 && memcmp(h.magic, "SVMB200M", 8) == 0 && h.version == 1 && h.d > 0 && h.d <= 1024 &&
+              h.pitch4 == (h.d + 3) / 4 && h.n_sv >= 0 && resolve_chunk(h.accum_chunk) > 0;
+    if (!ok) { fclose(f); FAIL(SVMB200_EINVAL, "%s is not a svmb200 model file (version 1)", path); }
+    const int nsv = h.n_sv, d = h.d;
+    std::vector<double> mn(d), mx(d), al(nsv), coef(nsv);
+    std::vector<int> ids(nsv), ys(nsv);
+    std::vector<float> rows((size_t)nsv * h.pitch4 * 4);
+    if (h.have_stats) ok = fread(mn.data(), sizeof(double), d, f) == (size_t)d && fread(mx.data(), sizeof(double), d, f) == (size_t)d;
+    ok = ok && fread(ids.data(), sizeof(int), nsv, f) == (size_t)nsv && fread(ys.data(), sizeof(int), nsv, f) == (size_t)nsv &&
+         fread(al.data(), sizeof(double), nsv, f) == (size_t)nsv && fread(rows.data(), sizeof(float), rows.size(), f) == rows.size();
+    fclose(f);
+    if (!ok) FAIL(SVMB200_EINVAL, "%s is truncated", path);
+    // the context now holds a model only: any training set is dropped
+    if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->sqn) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
+        dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv) || dev_free(ctx, ctx->svX) ||
+        dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn))
+        return SVMB200_ECUDA;
+    ctx->n = 0; ctx->d = d; ctx->pitch4 = h.pitch4; ctx->have_train = false; ctx->sqn_chunk = 0; ctx->sv_alloc = std::max(nsv, 1);
+    CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
+    CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
+    CK(cudaMalloc(&ctx->svX, (size_t)ctx->sv_alloc * h.pitch4 * 16));
+    CK(cudaMalloc(&ctx->svcoef, (size_t)ctx->sv_alloc * sizeof(double)));
+    CK(cudaMalloc(&ctx->svn, (size_t)ctx->sv_alloc * sizeof(double)));
+    if (h.have_stats) {
+        CK(cudaMemcpy(ctx->minv, mn.data(), (size_t)d * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(ctx->maxv, mx.data(), (size_t)d * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    for (int k = 0; k < nsv; ++k) coef[k] = al[k] * ys[k];
+    if (nsv) {
+        CK(cudaMemcpy(ctx->svX, rows.data(), rows.size() * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(ctx->svcoef, coef.data(), (size_t)nsv * sizeof(double), cudaMemcpyHostToDevice));
+        // norms of the SV rows, formed on the device by the same code as everywhere else
+        const int Q = q_for_pitch(h.pitch4);
+        cudaError_t e;
+        switch (h.accum_chunk) {
+        case 1: e = launch_sqnorm_q<1>(Q, ctx->svX, nsv, h.pitch4, ctx->svn, ctx->stream); break;
+        case 2: e = launch_sqnorm_q<2>(Q, ctx->svX, nsv, h.pitch4, ctx->svn, ctx->stream); break;
+        default: e = launch_sqnorm_q<4>(Q, ctx->svX, nsv, h.pitch4, ctx->svn, ctx->stream); break;
+        }
+        ctx->launches += 1;
+        CK(e);
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    svmb200_default_params(&ctx->params);
+    ctx->params.gamma = h.gamma; ctx->params.sv_tol = h.sv_tol; ctx->params.accum_chunk = h.accum_chunk;
+    ctx->b = h.b; ctx->have_stats = h.have_stats != 0;
+    ctx->sv_ids = ids; ctx->model_y = ys; ctx->alpha_host.clear();
+    ctx->model_nsv = nsv; ctx->model_ready = true; ctx->trained = true;
     return SVMB200_OK;
 }
 
@@ -744,6 +856,23 @@ extern "C" int svmb200_sv_ids(svmb200_ctx *ctx, int32_t *ids, int32_t cap, int32
     return SVMB200_OK;
 }
 
+// dense support-vector block (rows, norms, alpha*y) of the current model, built once per model
+static int ensure_model(svmb200_ctx *ctx)
+{
+    if (ctx->model_ready) return 0;
+    if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set to take the support vectors from");
+    std::vector<int> y_host(ctx->n);
+    CK(cudaMemcpyAsync(y_host.data(), ctx->y, (size_t)ctx->n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->model_y.resize(ctx->sv_ids.size());
+    for (size_t k = 0; k < ctx->model_y.size(); ++k) ctx->model_y[k] = y_host[ctx->sv_ids[k]];
+    if (int rc = ensure_norms(ctx, ctx->params.accum_chunk)) return rc;
+    if (int rc = build_sv_block(ctx, ctx->sv_ids, ctx->alpha_host.data(), ctx->model_y)) return rc;
+    ctx->model_nsv = (int)ctx->sv_ids.size();
+    ctx->model_ready = true;
+    return 0;
+}
+
 template <typename T>
 static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int64_t m, bool scale, int32_t ge_zero,
                         int32_t *correct, double *scores)
@@ -754,14 +883,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     if (scale && !ctx->have_stats) FAIL(SVMB200_ESTATE, "the training set was uploaded pre-scaled: use svmb200_predict_scaled_f64");
     CK(cudaSetDevice(ctx->device));
     const int pitch4 = ctx->pitch4;
-    // SV block (dense rows + coefficients)
-    std::vector<int> y_host(ctx->n);
-    CK(cudaMemcpyAsync(y_host.data(), ctx->y, (size_t)ctx->n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    std::vector<int> svy(ctx->sv_ids.size());
-    for (size_t k = 0; k < svy.size(); ++k) svy[k] = y_host[ctx->sv_ids[k]];
-    if (int rc = ensure_norms(ctx, ctx->params.accum_chunk)) return rc;
-    if (int rc = build_sv_block(ctx, ctx->sv_ids, ctx->alpha_host.data(), svy)) return rc;
+    if (int rc = ensure_model(ctx)) return rc;
 
     float *Xq = nullptr;
     double *dscores = nullptr;
@@ -773,7 +895,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     int rc = ingest<T>(ctx, X, m, false, scale, Xq);
     cudaError_t e = cudaSuccess;
     if (!rc) {
-        e = launch_decision_any(q_for_pitch(pitch4), ctx->params.accum_chunk, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, (int)ctx->sv_ids.size(),
+        e = launch_decision_any(q_for_pitch(pitch4), ctx->params.accum_chunk, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv,
                                 pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores, ctx->stream);
         ctx->launches += 1;
     }

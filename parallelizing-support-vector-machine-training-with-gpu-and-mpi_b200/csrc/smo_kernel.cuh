@@ -65,6 +65,7 @@ struct SmoArgs {
     unsigned long long policy_keep;    // L2 policy for the leading keep_frac of every warp's rows
     int keep_per_1024;                 // rows (per 1024) of each warp's range loaded with policy_keep
     int l2_ahead;                      // rows requested into L2 ahead of the shared-memory ring (0 = off)
+    int l2_burst;                      // rows per warp requested into L2 when the warp finishes its pass (0 = off)
     // ---- multi-GPU row sharding (peers == 1: single GPU) ----
     int peers;                          // GPUs sharing the rows
     int rank;                           // this GPU
@@ -581,6 +582,15 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
                     if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
                     best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                }
+            }
+            if (a.l2_burst > 0 && lane == 0 && m > KS + a.l2_burst) {
+                // the pass is over for this warp: the rows it will want right after the ring go from HBM to L2 while
+                // the CTAs are in the record exchange
+                int r = pf_row;
+                for (int k = 0; k < a.l2_burst; ++k) {
+                    bulk_prefetch_l2(a.X + (size_t)(w0 + r) * a.pitch4 * 4, (unsigned)row_bytes, a.policy_stream);
+                    if (++r == m) r = 0;
                 }
             }
         } else {

@@ -1,8 +1,3 @@
-set -x
-python bench.py --steps 2000 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err || { tail -5 gpurun_out/bench_n1.err; exit 1; }
-python bench.py --steps 300 --warmup 3 --no-cpu > gpurun_out/bench_small.json 2> gpurun_out/bench_small.err && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_r1.csv python bench.py --steps 300 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1
-python profiles/profile_target.py 60000 300 > gpurun_out/plain.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:smo_persistent -c 1 -o gpurun_out/prof_r1_smo60k_v2 python profiles/profile_target.py 60000 300 > gpurun_out/ncu_full.log 2>&1
-tail -2 gpurun_out/ncu_full.log
-python bench.py --impl reference --steps 2000 --warmup 3 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
+timeout 200 python -m pytest tests/test_gpu_parity.py -m gpu -x -q --tb=short --timeout 100 2>&1 | tail -3
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29520 profiles/cascade_bench.py 60000 2> gpurun_out/cascade8.err | grep -v NCCL | tee gpurun_out/cascade_r1_8gpu.jsonl
+tail -3 gpurun_out/cascade8.err | grep -v OMP

@@ -192,6 +192,32 @@ def test_predict_matches_oracle(solver, O, dataset):
     assert c_f64 == c_gpu and np.array_equal(s_f64, s_gpu)
 
 
+def test_model_save_and_load(solver, pkg, dataset, tmp_path):
+    """The model dump the reference left commented out (mpi_svm_main2.cpp:686-697), plus rows and statistics."""
+    X, _, y = dataset(700)
+    Xt, _, yt = dataset(300, split=1)
+    solver.set_train_u8(X, y)
+    out = solver.smo_train()
+    c0, s0 = solver.predict_u8(Xt, yt)
+    path = str(tmp_path / "model.svmb200")
+    solver.save_model(path)
+    fresh = pkg.Solver(0)
+    try:
+        fresh.load_model(path)
+        assert np.array_equal(fresh.sv_ids(), solver.sv_ids())
+        c1, s1 = fresh.predict_u8(Xt, yt)
+        assert c1 == c0 and np.array_equal(s1, s0)
+        with pytest.raises(pkg.SvmB200Error, match="before"):
+            fresh.n = 700
+            fresh.smo_train()
+        open(path, "r+b").write(b"garbage!")
+        with pytest.raises(pkg.SvmB200Error, match="not a svmb200 model"):
+            fresh.load_model(path)
+    finally:
+        fresh.close()
+    assert out["n_sv"] == len(solver.sv_ids())
+
+
 @pytest.mark.parametrize("d", [1, 4, 30, 100, 257, 1024])
 def test_other_feature_counts(solver, O, d):
     rng = np.random.default_rng(d)
