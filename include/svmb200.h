@@ -102,6 +102,12 @@ int svmb200_set_train_u8 (svmb200_ctx *ctx, const uint8_t *X, const int32_t *y, 
                           double *min_out, double *max_out);
 int svmb200_set_train_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y, int64_t n, int32_t d,
                           double *min_out, double *max_out);
+/* Storage precision of X for the NEXT svmb200_set_train_* call: 0 (default) = fp32 rows, the fast path the
+ * roofline numbers are quoted on; 1 = FP64 rows ("exact"): twice the bytes per iteration, K formed from FP64 squared
+ * differences as in main3.cpp:97-100, so that the selected (i_high, i_low) sequence is the reference's own
+ * (DESIGN.md "Numerics").  Exact storage takes d <= 832. */
+int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable);
+
 /* X already scaled by the caller -- exactly what the reference's SMO_train receives
  * (main3.cpp:347).  No statistics are computed; svmb200_predict_scaled_f64 is the matching call. */
 int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y, int64_t n, int32_t d);

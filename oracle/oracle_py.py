@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ARITH_F64, ARITH_DEVICE = 0, 1
+ARITH_F64, ARITH_DEVICE, ARITH_DEVICE_F64 = 0, 1, 2
 DEFAULT_CHUNK = 4   # the library's default svmb200_params.accum_chunk
 STOP_NAMES = {0: "converged", 1: "not_found", 2: "infeasible_uv", 3: "nonpositive_eta", 4: "max_iter"}
 
@@ -80,6 +80,8 @@ def lib():
         L.oracle_device_sqdist.restype = C.c_double
         L.oracle_device_sqdist.argtypes = [_f32(), _f32(), C.c_size_t]
         L.oracle_set_device_chunk.argtypes = [C.c_int]
+        L.oracle_device_kernel_f64.restype = C.c_double
+        L.oracle_device_kernel_f64.argtypes = [_f64(), _f64(), C.c_size_t, C.c_double]
         L.oracle_device_kernel.restype = C.c_double
         L.oracle_device_kernel.argtypes = [_f32(), _f32(), C.c_size_t, C.c_double]
         _lib = L

@@ -205,6 +205,31 @@ double oracle_device_kernel(const float *a, const float *b, size_t d, double gam
     return oracle_device_exp(-gamma * oracle_device_sqdist(a, b, d));
 }
 
+/* the exact path (svmb200_set_exact): FP64 rows, squared differences as in code/main3.cpp:97-100 but summed
+ * per lane (lane l = g mod 32 over the 16-byte groups g of two values) and combined by the same xor-butterfly */
+double oracle_device_kernel_f64(const double *a, const double *b, size_t d, double gamma)
+{
+    double lane[32];
+    for (int l = 0; l < 32; ++l) lane[l] = 0.0;
+    size_t groups = (d + 1) / 2;
+    for (size_t g = 0; g < groups; ++g) {
+        double acc = lane[g & 31];
+        for (int c = 0; c < 2; ++c) {
+            size_t k = 2 * g + c;
+            double av = k < d ? a[k] : 0.0, bv = k < d ? b[k] : 0.0;
+            double df = bv - av;
+            acc = fma(df, df, acc);
+        }
+        lane[g & 31] = acc;
+    }
+    for (int off = 16; off >= 1; off >>= 1) {
+        double t[32];
+        for (int l = 0; l < 32; ++l) t[l] = lane[l] + lane[l ^ off];
+        for (int l = 0; l < 32; ++l) lane[l] = t[l];
+    }
+    return oracle_device_exp(-gamma * lane[0]);
+}
+
 static double device_kernel_n(const float *a, const float *b, double na, double nb, size_t d, double gamma)
 {
     return oracle_device_exp(-gamma * oracle_device_sqdist_n(na, nb, oracle_device_dot(a, b, d)));
@@ -217,6 +242,9 @@ static void kernel_row(const double *x, const float *x32, const double *sqn, siz
     if (arith == ORACLE_ARITH_F64) {
         for (size_t j = 0; j < n; ++j)
             row[j] = oracle_kernel(x + i * d, x + j * d, d, gamma);
+    } else if (arith == ORACLE_ARITH_DEVICE_F64) {
+        for (size_t j = 0; j < n; ++j)
+            row[j] = oracle_device_kernel_f64(x + i * d, x + j * d, d, gamma);
     } else {
         for (size_t j = 0; j < n; ++j)
             row[j] = device_kernel_n(x32 + i * d, x32 + j * d, sqn[i], sqn[j], d, gamma);
@@ -253,9 +281,9 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
             double sum = 0.0;
             for (size_t j = 0; j < n; ++j) {
                 if (alpha[j] == 0.0) continue;
-                double kij = (arith == ORACLE_ARITH_F64)
-                                 ? oracle_kernel(x + j * d, x + i * d, d, gamma)
-                                 : device_kernel_n(x32 + j * d, x32 + i * d, sqn[j], sqn[i], d, gamma);
+                double kij = (arith == ORACLE_ARITH_F64)          ? oracle_kernel(x + j * d, x + i * d, d, gamma)
+                             : (arith == ORACLE_ARITH_DEVICE_F64) ? oracle_device_kernel_f64(x + j * d, x + i * d, d, gamma)
+                                                                  : device_kernel_n(x32 + j * d, x32 + i * d, sqn[j], sqn[i], d, gamma);
                 sum += alpha[j] * y[j] * kij;
             }
             f[i] = sum - (double)y[i];
@@ -366,9 +394,9 @@ int oracle_predict(const double *x_test, const int *y_test, size_t m,
         double curr = -b;
         for (size_t k = 0; k < n_sv; ++k) {
             size_t j = (size_t)sv_idx[k];
-            double kv = (arith == ORACLE_ARITH_F64)
-                            ? oracle_kernel(x_test + i * d, x_train + j * d, d, gamma)
-                            : oracle_device_kernel(t32 + i * d, s32 + k * d, d, gamma);
+            double kv = (arith == ORACLE_ARITH_F64)          ? oracle_kernel(x_test + i * d, x_train + j * d, d, gamma)
+                        : (arith == ORACLE_ARITH_DEVICE_F64) ? oracle_device_kernel_f64(x_test + i * d, x_train + j * d, d, gamma)
+                                                             : oracle_device_kernel(t32 + i * d, s32 + k * d, d, gamma);
             curr += alpha[j] * y_train[j] * kv;
         }
         if (scores) scores[i] = curr;

@@ -45,9 +45,11 @@ enum {
 /* how kernel rows are evaluated */
 enum {
     ORACLE_ARITH_F64      = 0, /* the reference's arithmetic: sequential FP64 sum, libm exp */
-    ORACLE_ARITH_DEVICE   = 1  /* the CUDA path's arithmetic restated op for op (fp32 X,
+    ORACLE_ARITH_DEVICE   = 1, /* the CUDA path's arithmetic restated op for op (fp32 X,
                                   squared norms + fp32-chunk dot products, FP64 lane sums,
                                   fixed butterfly order, svm_exp): used to check the GPU bit for bit */
+    ORACLE_ARITH_DEVICE_F64 = 2 /* the CUDA exact path (svmb200_set_exact: FP64 rows, squared
+                                  differences, per-lane FP64 sums, same butterfly, svm_exp) */
 };
 
 typedef struct {
@@ -105,6 +107,7 @@ double oracle_device_dot(const float *a, const float *b, size_t d);
 double oracle_device_sqdist_n(double na, double nb, double ab);
 double oracle_device_sqdist(const float *a, const float *b, size_t d);
 double oracle_device_kernel(const float *a, const float *b, size_t d, double gamma);
+double oracle_device_kernel_f64(const double *a, const double *b, size_t d, double gamma);
 
 #ifdef __cplusplus
 }

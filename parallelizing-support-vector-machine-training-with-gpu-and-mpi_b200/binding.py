@@ -73,6 +73,7 @@ def load_library():
     L.svmb200_set_train_u8.argtypes = [vp, vp, vp, i64, i32, vp, vp]
     L.svmb200_set_train_f64.argtypes = [vp, vp, vp, i64, i32, vp, vp]
     L.svmb200_set_train_scaled_f64.argtypes = [vp, vp, vp, i64, i32]
+    L.svmb200_set_exact.argtypes = [vp, i32]
     L.svmb200_minmax_f64.argtypes = [vp, vp, i64, i32, vp, vp]
     L.svmb200_scale_f64.argtypes = [vp, vp, vp, vp, i64, i32]
     L.svmb200_smo_train.argtypes = [vp, C.POINTER(Params), vp, C.POINTER(dbl), C.POINTER(Stats)]
@@ -135,6 +136,10 @@ class Solver:
             raise SvmB200Error(f"{what} = {rc}: {self.L.svmb200_last_error(self.h).decode()}")
 
     # ---- ingest
+    def set_exact(self, enable: bool):
+        """FP64 storage of X for the next set_train_* (the exact path); False = fp32 (default)."""
+        self._ck(self.L.svmb200_set_exact(self.h, 1 if enable else 0), "set_exact")
+
     def set_train_u8(self, X, y):
         X = np.ascontiguousarray(X, dtype=np.uint8)
         y = np.ascontiguousarray(y, dtype=np.int32)

@@ -45,19 +45,19 @@ __global__ void colminmax_final_kernel(const double *__restrict__ pmin, const do
 
 // ---- scale + narrow + pad: replaces scale_features (code/main3.cpp:74-89): (x - min) / range in
 // FP64 with range < 1e-12 -> 1, then rounded once to fp32.  minv == nullptr: X is already scaled.
-template <typename T>
-__global__ void scale_to_f32_kernel(const T *__restrict__ X, long long n, int d, int pitch4,
-                                    const double *__restrict__ minv, const double *__restrict__ maxv,
-                                    float *__restrict__ out)
+template <typename T, typename XT>
+__global__ void scale_rows_kernel(const T *__restrict__ X, long long n, int d, int pitch4,
+                                  const double *__restrict__ minv, const double *__restrict__ maxv,
+                                  XT *__restrict__ out)
 {
+    constexpr int PER = 16 / (int)sizeof(XT);            // values per 16-byte group: 4 fp32 or 2 FP64
     const long long total = n * pitch4;
     for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
         const long long r = g / pitch4;
         const int q = (int)(g - r * pitch4);
-        float v[4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const int col = 4 * q + c;
+        for (int c = 0; c < PER; ++c) {
+            const int col = PER * q + c;
             double x = 0.0;
             if (col < d) {
                 x = (double)X[r * d + col];
@@ -67,9 +67,8 @@ __global__ void scale_to_f32_kernel(const T *__restrict__ X, long long n, int d,
                     x = (x - minv[col]) / range;
                 }
             }
-            v[c] = (float)x;
+            out[g * PER + c] = (XT)x;                      // fp32: the one rounding of the fast path; FP64: the reference's value
         }
-        reinterpret_cast<float4 *>(out)[g] = make_float4(v[0], v[1], v[2], v[3]);
     }
 }
 
@@ -99,7 +98,7 @@ __global__ void row_sqnorm_kernel(const float *__restrict__ X, long long n, int 
 #pragma unroll
     for (int i = 0; i < Q; ++i) {
         const int q = i * 32 + lane;
-        if (q < pitch4) { const float4 v = __ldg(xj + q); accum_dot<CH>(v, v, acc); }
+        if (q < pitch4) { const float4 v = __ldg(xj + q); accum_dot<CH>(v, v, acc); }   // fp32 rows only: FP64 rows need no norms
     }
     acc = warp_sum_butterfly(acc);
     if (lane == 0) sqn[j] = acc;
@@ -117,10 +116,10 @@ __global__ void init_state_kernel(const int *__restrict__ y, long long n, double
 }
 
 // ---- gather rows (support vectors) and their squared norms into a dense block
-__global__ void gather_rows_kernel(const float *__restrict__ X, const double *__restrict__ sqn, int pitch4,
-                                   const int *__restrict__ ids, int count, float *__restrict__ out, double *__restrict__ out_n)
+__global__ void gather_rows_kernel(const void *__restrict__ X, const double *__restrict__ sqn, int pitch4,
+                                   const int *__restrict__ ids, int count, void *__restrict__ out, double *__restrict__ out_n)
 {
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) out_n[k] = sqn[ids[k]];
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) out_n[k] = sqn ? sqn[ids[k]] : 0.0;
     const long long total = (long long)count * pitch4;
     for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
         const long long k = g / pitch4;
@@ -140,9 +139,9 @@ constexpr int DEC_THREADS = 512;
 constexpr int DEC_WARPS = DEC_THREADS / 32;
 constexpr int DEC_TILE = 16;
 
-template <int Q, int CH>
+template <typename XT, int Q, int CH>
 __global__ void __launch_bounds__(DEC_THREADS, 1)
-decision_kernel(const float *__restrict__ Xq, long long m, const float *__restrict__ SV, const double *__restrict__ svn,
+decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict__ SV, const double *__restrict__ svn,
                 const double *__restrict__ coef, int nsv, int pitch4, double gamma, double init, const int *__restrict__ ysub, double *__restrict__ out)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -158,26 +157,28 @@ decision_kernel(const float *__restrict__ Xq, long long m, const float *__restri
     }
     __syncthreads();
 
+    using Vec = typename RowVec<XT>::type;
     const long long qi = (long long)blockIdx.x * DEC_WARPS + warp;
     const bool active = qi < m;
-    float4 qv[Q];
+    Vec qv[Q];
 #pragma unroll
     for (int i = 0; i < Q; ++i) {
         const int q = i * 32 + lane;
-        qv[i] = (active && q < pitch4) ? __ldg(reinterpret_cast<const float4 *>(Xq) + (size_t)qi * pitch4 + q)
-                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+        qv[i] = (active && q < pitch4) ? __ldg(reinterpret_cast<const Vec *>(Xq) + (size_t)qi * pitch4 + q) : vec_zero<Vec>();
     }
-    double qn = 0.0;                                                   // |q|^2, the same way the solver forms norms
+    double qn = 0.0;                                                   // |q|^2, the same way the solver forms norms (fp32 rows)
+    if (sizeof(XT) == 4) {
 #pragma unroll
-    for (int i = 0; i < Q; ++i)
-        if (i * 32 + lane < pitch4) accum_dot<CH>(qv[i], qv[i], qn);
-    qn = warp_sum_butterfly(qn);
+        for (int i = 0; i < Q; ++i)
+            if (i * 32 + lane < pitch4) accum_pair<CH>(qv[i], qv[i], qn);
+        qn = warp_sum_butterfly(qn);
+    }
 
     const int ntiles = (nsv + DEC_TILE - 1) / DEC_TILE;
     auto issue_tile = [&](int t) {      // thread 0
         const int rows = min(DEC_TILE, nsv - t * DEC_TILE);
         mbar_expect_tx(&bars[t & 1], (unsigned)(rows * row_bytes));
-        bulk_g2s(tiles + (size_t)(t & 1) * DEC_TILE * row_bytes, SV + (size_t)t * DEC_TILE * pitch4 * 4,
+        bulk_g2s(tiles + (size_t)(t & 1) * DEC_TILE * row_bytes, static_cast<const unsigned char *>(SV) + (size_t)t * DEC_TILE * row_bytes,
                  (unsigned)(rows * row_bytes), &bars[t & 1], L2_EVICT_LAST);
     };
     if (threadIdx.x == 0 && ntiles > 0) issue_tile(0);
@@ -190,18 +191,18 @@ decision_kernel(const float *__restrict__ Xq, long long m, const float *__restri
         const unsigned char *tile = tiles + (size_t)(t & 1) * DEC_TILE * row_bytes;
         double myk = 0.0;
         for (int r = 0; r < rows; ++r) {
-            const float4 *row = reinterpret_cast<const float4 *>(tile + (size_t)r * row_bytes);
+            const Vec *row = reinterpret_cast<const Vec *>(tile + (size_t)r * row_bytes);
             double acc = 0.0;
 #pragma unroll
             for (int i = 0; i < Q; ++i) {
                 const int q = i * 32 + lane;
-                if (q < pitch4) accum_dot<CH>(row[q], qv[i], acc);
+                if (q < pitch4) accum_pair<CH>(row[q], qv[i], acc);
             }
             acc = warp_sum_butterfly(acc);
             if (lane == r) myk = acc;
         }
-        const double myn = lane < rows ? svn[t * DEC_TILE + lane] : 0.0;
-        myk = svm_exp(-gamma * sqdist_from_dot(qn, myn, myk));        // lanes >= rows compute a value nobody reads
+        const double myn = (sizeof(XT) == 4 && lane < rows) ? svn[t * DEC_TILE + lane] : 0.0;
+        myk = svm_exp(-gamma * dist2<XT>(qn, myn, myk));        // lanes >= rows compute a value nobody reads
         const double mycoef = lane < rows ? coef[t * DEC_TILE + lane] : 0.0;
         for (int r = 0; r < rows; ++r) {
             const double k = __shfl_sync(FULL, myk, r);
@@ -235,23 +236,24 @@ __global__ void count_correct_kernel(const double *__restrict__ scores, const in
 }
 
 // ---- introspection: one kernel row exactly as the solver forms it (a warp per row, no staging)
-template <int Q, int CH>
-__global__ void kernel_row_kernel(const float *__restrict__ X, const double *__restrict__ sqn, long long n, int pitch4,
+template <typename XT, int Q, int CH>
+__global__ void kernel_row_kernel(const void *__restrict__ X, const double *__restrict__ sqn, long long n, int pitch4,
                                   long long pivot, double gamma, double *__restrict__ out)
 {
     const int lane = threadIdx.x & 31;
     const long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (j >= n) return;
-    const float4 *xp = reinterpret_cast<const float4 *>(X) + (size_t)pivot * pitch4;
-    const float4 *xj = reinterpret_cast<const float4 *>(X) + (size_t)j * pitch4;
+    using Vec = typename RowVec<XT>::type;
+    const Vec *xp = reinterpret_cast<const Vec *>(X) + (size_t)pivot * pitch4;
+    const Vec *xj = reinterpret_cast<const Vec *>(X) + (size_t)j * pitch4;
     double acc = 0.0;
 #pragma unroll
     for (int i = 0; i < Q; ++i) {
         const int q = i * 32 + lane;
-        if (q < pitch4) accum_dot<CH>(__ldg(xj + q), __ldg(xp + q), acc);
+        if (q < pitch4) accum_pair<CH>(__ldg(xj + q), __ldg(xp + q), acc);
     }
     acc = warp_sum_butterfly(acc);
-    if (lane == 0) out[j] = svm_exp(-gamma * sqdist_from_dot(sqn[pivot], sqn[j], acc));
+    if (lane == 0) out[j] = svm_exp(-gamma * dist2<XT>(sizeof(XT) == 4 ? sqn[pivot] : 0.0, sizeof(XT) == 4 ? sqn[j] : 0.0, acc));
 }
 
 // ---- introspection: one working-set selection with the solver's own compare (single CTA)

@@ -42,7 +42,8 @@ struct svmb200_ctx {
     // training set
     long long n = 0;
     int d = 0, pitch4 = 0;
-    float *X = nullptr;
+    void *X = nullptr;          // fp32 rows, or FP64 rows when x_f64
+    bool exact_requested = false, x_f64 = false;
     int *y = nullptr;
     double *sqn = nullptr;      // |x_j|^2 formed with accumulation chunk sqn_chunk (0 = not computed)
     int sqn_chunk = 0;
@@ -66,7 +67,7 @@ struct svmb200_ctx {
     double b = 0.0;
     std::vector<double> alpha_host;
     std::vector<int> sv_ids;
-    float *svX = nullptr;
+    void *svX = nullptr;
     double *svcoef = nullptr;
     double *svn = nullptr;
     bool model_ready = false;   // svX / svcoef / svn hold the support vectors of the current model
@@ -204,15 +205,19 @@ void svmb200_destroy(svmb200_ctx *ctx)
 
 } // extern "C"
 
+static int max_pitch(bool f64) { return f64 ? 13 * 32 : 8 * 32; }   // 16-byte groups per row the pivot registers can hold
+
 // ------------------------------------------------------------------------------------------
 static int alloc_train(svmb200_ctx *ctx, long long n, int d)
 {
     if (n <= 0 || d <= 0) FAIL(SVMB200_EINVAL, "n and d must be positive (n=%lld d=%d)", n, d);
     if (n >= 0x7fffffffLL) FAIL(SVMB200_ELIMIT, "n=%lld exceeds the 2^31-2 row limit", n);
-    const int pitch4 = (d + 3) / 4;
-    if (pitch4 > 256) FAIL(SVMB200_ELIMIT, "d=%d exceeds the 1024-feature limit of the in-register pivot rows", d);
+    const bool f64 = ctx->exact_requested;
+    const int pitch4 = f64 ? (d + 1) / 2 : (d + 3) / 4;          // 16-byte groups per row
+    if (pitch4 > max_pitch(f64))
+        FAIL(SVMB200_ELIMIT, "d=%d exceeds the %d-feature limit of the in-register pivot rows", d, f64 ? 832 : 1024);
     CK(cudaSetDevice(ctx->device));
-    if (n != ctx->n || d != ctx->d) {
+    if (n != ctx->n || d != ctx->d || f64 != ctx->x_f64) {
         if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->sqn) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
             dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv))
             return SVMB200_ECUDA;
@@ -227,6 +232,7 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
         ctx->n = n;
         ctx->d = d;
         ctx->pitch4 = pitch4;
+        ctx->x_f64 = f64;
     }
     ctx->have_train = false;
     ctx->trained = false;
@@ -238,7 +244,7 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
 
 // stage raw host rows in device scratch, compute statistics (optional), scale into dst
 template <typename T>
-static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool compute_stats, bool apply_stats, float *dst)
+static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool compute_stats, bool apply_stats, void *dst)
 {
     const int d = ctx->d, pitch4 = ctx->pitch4;
     const size_t raw_bytes = (size_t)rows * d * sizeof(T);
@@ -258,8 +264,12 @@ static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool comput
     }
     const long long total = rows * pitch4;
     const int blocks = (int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16);
-    scale_to_f32_kernel<T><<<blocks, 256, 0, ctx->stream>>>(raw, rows, d, pitch4, apply_stats ? ctx->minv : nullptr,
-                                                            apply_stats ? ctx->maxv : nullptr, dst);
+    if (ctx->x_f64)
+        scale_rows_kernel<T, double><<<blocks, 256, 0, ctx->stream>>>(raw, rows, d, pitch4, apply_stats ? ctx->minv : nullptr,
+                                                                      apply_stats ? ctx->maxv : nullptr, static_cast<double *>(dst));
+    else
+        scale_rows_kernel<T, float><<<blocks, 256, 0, ctx->stream>>>(raw, rows, d, pitch4, apply_stats ? ctx->minv : nullptr,
+                                                                     apply_stats ? ctx->maxv : nullptr, static_cast<float *>(dst));
     ctx->launches += 1;
     CK(cudaGetLastError());
     return 0;
@@ -300,6 +310,14 @@ int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32
 }
 
 } // extern "C"
+
+// storage precision of X for the NEXT svmb200_set_train_*: 0 = fp32 (default), 1 = FP64 ("exact")
+extern "C" int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    ctx->exact_requested = enable != 0;
+    return SVMB200_OK;
+}
 
 extern "C" int svmb200_minmax_f64(svmb200_ctx *ctx, const double *X, int64_t n, int32_t d, double *min_out, double *max_out)
 {
@@ -344,135 +362,104 @@ extern "C" int svmb200_scale_f64(svmb200_ctx *ctx, double *X, const double *min_
 }
 
 // ------------------------------------------------------------------------------------------
-static int q_for_pitch(int pitch4)
+// Kernel dispatch.  Q = 16-byte groups per lane per row (the pivot rows live in registers, so Q is a template
+// parameter); fp32 rows: Q in {1,2,4,7,8} (d <= 1024), FP64 rows ("exact" storage): Q in {1,2,4,7,13} (d <= 832).
+static int q_for_pitch(int pitch4, bool f64)
 {
     const int need = (pitch4 + 31) / 32;
     if (need <= 1) return 1;
     if (need <= 2) return 2;
     if (need <= 4) return 4;
-    if (need <= 7) return need == 7 ? 7 : 8;
-    return 8;
+    if (need <= 7) return 7;
+    return f64 ? 13 : 8;
 }
 
-template <int Q, int CH, int THREADS>
-static cudaError_t launch_smo(const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
-{
-    cudaError_t e = cudaFuncSetAttribute(smo_persistent_kernel<Q, CH, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    void *kargs[] = {(void *)&args};
-    return cudaLaunchCooperativeKernel((void *)smo_persistent_kernel<Q, CH, THREADS>, dim3(grid), dim3(THREADS), kargs, smem, stream);
-}
+struct KernelKey { bool f64; int Q, CH, threads; };
 
-// CTA sizes other than 512 threads exist for the MNIST-shaped rows only (Q = 7)
-template <int CH>
-static cudaError_t launch_smo_q(int Q, int threads, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+// calls fn.template operator()<XT, Q, CH, THREADS>() for the instantiation the key names
+template <typename F>
+static cudaError_t dispatch(const KernelKey &k, F &&fn)
 {
-    switch (Q) {
-    case 1: return launch_smo<1, CH, 512>(args, grid, smem, stream);
-    case 2: return launch_smo<2, CH, 512>(args, grid, smem, stream);
-    case 4: return launch_smo<4, CH, 512>(args, grid, smem, stream);
+    if (k.f64) {                      // FP64 rows: 384 threads (pivot rows take 104 registers at Q = 13), no accumulation chunk
+        switch (k.Q) {
+        case 1: return fn.template operator()<double, 1, 1, 384>();
+        case 2: return fn.template operator()<double, 2, 1, 384>();
+        case 4: return fn.template operator()<double, 4, 1, 384>();
+        case 7: return fn.template operator()<double, 7, 1, 384>();
+        default: return fn.template operator()<double, 13, 1, 384>();
+        }
+    }
+#define SVM_F32_CASE(QQ, TT)                                                    \
+    switch (k.CH) {                                                              \
+    case 1: return fn.template operator()<float, QQ, 1, TT>();                   \
+    case 2: return fn.template operator()<float, QQ, 2, TT>();                   \
+    default: return fn.template operator()<float, QQ, 4, TT>();                  \
+    }
+    switch (k.Q) {
+    case 1: SVM_F32_CASE(1, 512)
+    case 2: SVM_F32_CASE(2, 512)
+    case 4: SVM_F32_CASE(4, 512)
     case 7:
-        if (threads == 256) return launch_smo<7, CH, 256>(args, grid, smem, stream);
-        if (threads == 384) return launch_smo<7, CH, 384>(args, grid, smem, stream);
-        return launch_smo<7, CH, 512>(args, grid, smem, stream);
-    default: return launch_smo<8, CH, 512>(args, grid, smem, stream);
+        if (k.threads == 256) { SVM_F32_CASE(7, 256) }
+        if (k.threads == 384) { SVM_F32_CASE(7, 384) }
+        SVM_F32_CASE(7, 512)
+    default: SVM_F32_CASE(8, 512)
     }
+#undef SVM_F32_CASE
 }
 
-static cudaError_t launch_smo_any(int Q, int CH, int threads, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+static cudaError_t launch_smo_any(const KernelKey &k, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
 {
-    switch (CH) {
-    case 1: return launch_smo_q<1>(Q, threads, args, grid, smem, stream);
-    case 2: return launch_smo_q<2>(Q, threads, args, grid, smem, stream);
-    default: return launch_smo_q<4>(Q, threads, args, grid, smem, stream);
-    }
+    return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(smo_persistent_kernel<XT, Q, CH, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        void *kargs[] = {(void *)&args};
+        return cudaLaunchCooperativeKernel((void *)smo_persistent_kernel<XT, Q, CH, THREADS>, dim3(grid), dim3(THREADS), kargs, smem, stream);
+    });
 }
 
-template <int Q, int CH>
-static cudaError_t launch_decision(const float *Xq, long long m, const float *SV, const double *svn, const double *coef, int nsv, int pitch4,
-                                   double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
+static cudaError_t launch_decision_any(KernelKey k, const void *Xq, long long m, const void *SV, const double *svn, const double *coef,
+                                       int nsv, int pitch4, double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
 {
-    const size_t smem = decision_smem_bytes(pitch4);
-    cudaError_t e = cudaFuncSetAttribute(decision_kernel<Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    const int grid = (int)((m + DEC_WARPS - 1) / DEC_WARPS);
-    decision_kernel<Q, CH><<<grid, DEC_THREADS, smem, stream>>>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out);
-    return cudaGetLastError();
+    k.threads = k.f64 ? 384 : 512;      // one instantiation per (XT, Q, CH): the CTA size of this kernel is fixed
+    return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
+        const size_t smem = decision_smem_bytes(pitch4);
+        cudaError_t e = cudaFuncSetAttribute(decision_kernel<XT, Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        const int grid = (int)((m + DEC_WARPS - 1) / DEC_WARPS);
+        decision_kernel<XT, Q, CH><<<grid, DEC_THREADS, smem, stream>>>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out);
+        return cudaGetLastError();
+    });
 }
 
-template <int CH>
-static cudaError_t launch_decision_q(int Q, const float *Xq, long long m, const float *SV, const double *svn, const double *coef, int nsv,
-                                     int pitch4, double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
+static cudaError_t launch_krow_any(KernelKey k, const void *X, const double *sqn, long long n, int pitch4, long long pivot, double gamma,
+                                   double *out, cudaStream_t s)
 {
-    switch (Q) {
-    case 1: return launch_decision<1, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 2: return launch_decision<2, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 4: return launch_decision<4, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 7: return launch_decision<7, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    default: return launch_decision<8, CH>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    }
+    k.threads = k.f64 ? 384 : 512;
+    return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
+        const long long threads = n * 32;
+        kernel_row_kernel<XT, Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, sqn, n, pitch4, pivot, gamma, out);
+        return cudaGetLastError();
+    });
 }
 
-static cudaError_t launch_decision_any(int Q, int CH, const float *Xq, long long m, const float *SV, const double *svn, const double *coef,
-                                       int nsv, int pitch4, double gamma, double init, const int *ysub, double *out,
-                                       cudaStream_t stream)
+static cudaError_t launch_sqnorm_any(KernelKey k, const float *X, long long n, int pitch4, double *sqn, cudaStream_t s)
 {
-    switch (CH) {
-    case 1: return launch_decision_q<1>(Q, Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    case 2: return launch_decision_q<2>(Q, Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    default: return launch_decision_q<4>(Q, Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, stream);
-    }
+    k.threads = 512;
+    k.f64 = false;
+    return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
+        const long long threads = n * 32;
+        row_sqnorm_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, n, pitch4, sqn);
+        return cudaGetLastError();
+    });
 }
 
-template <int Q, int CH>
-static cudaError_t launch_krow(const float *X, const double *sqn, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
-{
-    const long long threads = n * 32;
-    kernel_row_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, sqn, n, pitch4, pivot, gamma, out);
-    return cudaGetLastError();
-}
-template <int CH>
-static cudaError_t launch_krow_q(int Q, const float *X, const double *sqn, long long n, int pitch4, long long pivot, double gamma, double *out, cudaStream_t s)
-{
-    switch (Q) {
-    case 1: return launch_krow<1, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
-    case 2: return launch_krow<2, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
-    case 4: return launch_krow<4, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
-    case 7: return launch_krow<7, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
-    default: return launch_krow<8, CH>(X, sqn, n, pitch4, pivot, gamma, out, s);
-    }
-}
-
-template <int Q, int CH>
-static cudaError_t launch_sqnorm(const float *X, long long n, int pitch4, double *sqn, cudaStream_t s)
-{
-    const long long threads = n * 32;
-    row_sqnorm_kernel<Q, CH><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(X, n, pitch4, sqn);
-    return cudaGetLastError();
-}
-template <int CH>
-static cudaError_t launch_sqnorm_q(int Q, const float *X, long long n, int pitch4, double *sqn, cudaStream_t s)
-{
-    switch (Q) {
-    case 1: return launch_sqnorm<1, CH>(X, n, pitch4, sqn, s);
-    case 2: return launch_sqnorm<2, CH>(X, n, pitch4, sqn, s);
-    case 4: return launch_sqnorm<4, CH>(X, n, pitch4, sqn, s);
-    case 7: return launch_sqnorm<7, CH>(X, n, pitch4, sqn, s);
-    default: return launch_sqnorm<8, CH>(X, n, pitch4, sqn, s);
-    }
-}
-static int q_for_pitch(int pitch4);
-// squared norms of the training rows for accumulation chunk CH (recomputed only when CH changes)
+// squared norms of the fp32 training rows for accumulation chunk CH (recomputed only when CH changes)
 static int ensure_norms(svmb200_ctx *ctx, int CH)
 {
-    if (ctx->sqn_chunk == CH) return 0;
-    const int Q = q_for_pitch(ctx->pitch4);
-    cudaError_t e;
-    switch (CH) {
-    case 1: e = launch_sqnorm_q<1>(Q, ctx->X, ctx->n, ctx->pitch4, ctx->sqn, ctx->stream); break;
-    case 2: e = launch_sqnorm_q<2>(Q, ctx->X, ctx->n, ctx->pitch4, ctx->sqn, ctx->stream); break;
-    default: e = launch_sqnorm_q<4>(Q, ctx->X, ctx->n, ctx->pitch4, ctx->sqn, ctx->stream); break;
-    }
+    if (ctx->x_f64 || ctx->sqn_chunk == CH) return 0;
+    KernelKey k{false, q_for_pitch(ctx->pitch4, false), CH, 512};
+    cudaError_t e = launch_sqnorm_any(k, static_cast<const float *>(ctx->X), ctx->n, ctx->pitch4, ctx->sqn, ctx->stream);
     ctx->launches += 1;
     CK(e);
     ctx->sqn_chunk = CH;
@@ -508,7 +495,7 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
     CK(cudaMemcpyAsync(ctx->svcoef, coef.data(), (size_t)nsv * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     const long long total = (long long)nsv * ctx->pitch4;
     gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
-        ctx->X, ctx->sqn, ctx->pitch4, static_cast<const int *>(ctx->scratch), nsv, ctx->svX, ctx->svn);
+        ctx->X, ctx->x_f64 ? nullptr : ctx->sqn, ctx->pitch4, static_cast<const int *>(ctx->scratch), nsv, ctx->svX, ctx->svn);
     ctx->launches += 1;
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));   // coef / ids are host temporaries
@@ -529,9 +516,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const int launches0 = ctx->launches;
 
     // persistent grid: one CTA per SM, fewer for tiny problems
-    const int Q = q_for_pitch(ctx->pitch4);
-    int threads = 512;
-    if (Q == 7) {
+    const int Q = q_for_pitch(ctx->pitch4, ctx->x_f64);
+    int threads = ctx->x_f64 ? 384 : 512;
+    if (Q == 7 && !ctx->x_f64) {
         threads = SMO_DEFAULT_THREADS_Q7;
         if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py
             const int t = atoi(e);
@@ -592,7 +579,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 0, 0);
         ctx->launches += 1;
         CK(cudaGetLastError());
-        CK(launch_decision_any(Q, CH, ctx->X, n, ctx->svX, ctx->svn, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
+        CK(launch_decision_any(KernelKey{ctx->x_f64, Q, CH, 0}, ctx->X, n, ctx->svX, ctx->svn, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
                                ctx->y, ctx->f, ctx->stream));
         ctx->launches += 1;
     } else {
@@ -602,7 +589,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
 
     SmoArgs a{};
-    a.X = ctx->X; a.sqn = ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
+    a.X = ctx->X; a.sqn = ctx->x_f64 ? nullptr : ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
     a.cacheq = cache_cap > 0 ? ctx->cacheq : nullptr;
     a.cacheK = ctx->cacheK; a.rec = ctx->rec;
     a.arrive = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
@@ -642,7 +629,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 #endif
 
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(launch_smo_any(Q, CH, threads, a, grid, smem, ctx->stream));
+    CK(launch_smo_any(KernelKey{ctx->x_f64, Q, CH, threads}, a, grid, smem, ctx->stream));
     ctx->launches += 1;
     CK(cudaEventRecord(ctx->ev2, ctx->stream));
 
@@ -750,7 +737,7 @@ namespace {
 struct ModelHeader {
     char magic[8];          // "SVMB200M"
     uint32_t version;
-    int32_t d, pitch4, n_sv, accum_chunk, have_stats;
+    int32_t d, pitch4, n_sv, accum_chunk, have_stats, x_f64, reserved;
     double gamma, b, sv_tol;
 };
 }
@@ -764,7 +751,7 @@ extern "C" int svmb200_save_model(svmb200_ctx *ctx, const char *path)
     const int nsv = ctx->model_nsv;
     ModelHeader h{};
     memcpy(h.magic, "SVMB200M", 8);
-    h.version = 1; h.d = ctx->d; h.pitch4 = ctx->pitch4; h.n_sv = nsv; h.accum_chunk = ctx->params.accum_chunk;
+    h.version = 2; h.x_f64 = ctx->x_f64 ? 1 : 0; h.d = ctx->d; h.pitch4 = ctx->pitch4; h.n_sv = nsv; h.accum_chunk = ctx->params.accum_chunk;
     h.have_stats = ctx->have_stats ? 1 : 0; h.gamma = ctx->params.gamma; h.b = ctx->b; h.sv_tol = ctx->params.sv_tol;
     std::vector<double> mn(ctx->d), mx(ctx->d), al(nsv);
     std::vector<float> rows((size_t)nsv * ctx->pitch4 * 4);
@@ -792,9 +779,9 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
     FILE *f = fopen(path, "rb");
     if (!f) FAIL(SVMB200_EINVAL, "cannot open %s", path);
     ModelHeader h{};
-    bool ok = fread(&h, sizeof h, 1, f) == 1 && memcmp(h.magic, "SVMB200M", 8) == 0 && h.version == 1 && h.d > 0 && h.d <= 1024 &&
-              h.pitch4 == (h.d + 3) / 4 && h.n_sv >= 0 && resolve_chunk(h.accum_chunk) > 0;
-    if (!ok) { fclose(f); FAIL(SVMB200_EINVAL, "%s is not a svmb200 model file (version 1)", path); }
+    bool ok = fread(&h, sizeof h, 1, f) == 1 && memcmp(h.magic, "SVMB200M", 8) == 0 && h.version == 2 && h.d > 0 && h.d <= 1024 &&
+              h.pitch4 == (h.x_f64 ? (h.d + 1) / 2 : (h.d + 3) / 4) && h.pitch4 <= max_pitch(h.x_f64 != 0) && h.n_sv >= 0 && resolve_chunk(h.accum_chunk) > 0;
+    if (!ok) { fclose(f); FAIL(SVMB200_EINVAL, "%s is not a svmb200 model file (version 2)", path); }
     const int nsv = h.n_sv, d = h.d;
     std::vector<double> mn(d), mx(d), al(nsv), coef(nsv);
     std::vector<int> ids(nsv), ys(nsv);
@@ -809,7 +796,7 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
         dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv) || dev_free(ctx, ctx->svX) ||
         dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn))
         return SVMB200_ECUDA;
-    ctx->n = 0; ctx->d = d; ctx->pitch4 = h.pitch4; ctx->have_train = false; ctx->sqn_chunk = 0; ctx->sv_alloc = std::max(nsv, 1);
+    ctx->n = 0; ctx->d = d; ctx->pitch4 = h.pitch4; ctx->x_f64 = h.x_f64 != 0; ctx->have_train = false; ctx->sqn_chunk = 0; ctx->sv_alloc = std::max(nsv, 1);
     CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
     CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
     CK(cudaMalloc(&ctx->svX, (size_t)ctx->sv_alloc * h.pitch4 * 16));
@@ -823,16 +810,13 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
     if (nsv) {
         CK(cudaMemcpy(ctx->svX, rows.data(), rows.size() * sizeof(float), cudaMemcpyHostToDevice));
         CK(cudaMemcpy(ctx->svcoef, coef.data(), (size_t)nsv * sizeof(double), cudaMemcpyHostToDevice));
-        // norms of the SV rows, formed on the device by the same code as everywhere else
-        const int Q = q_for_pitch(h.pitch4);
-        cudaError_t e;
-        switch (h.accum_chunk) {
-        case 1: e = launch_sqnorm_q<1>(Q, ctx->svX, nsv, h.pitch4, ctx->svn, ctx->stream); break;
-        case 2: e = launch_sqnorm_q<2>(Q, ctx->svX, nsv, h.pitch4, ctx->svn, ctx->stream); break;
-        default: e = launch_sqnorm_q<4>(Q, ctx->svX, nsv, h.pitch4, ctx->svn, ctx->stream); break;
+        // norms of the SV rows (fp32 storage), formed on the device by the same code as everywhere else
+        if (!h.x_f64) {
+            cudaError_t e = launch_sqnorm_any(KernelKey{false, q_for_pitch(h.pitch4, false), h.accum_chunk, 512},
+                                              static_cast<const float *>(ctx->svX), nsv, h.pitch4, ctx->svn, ctx->stream);
+            ctx->launches += 1;
+            CK(e);
         }
-        ctx->launches += 1;
-        CK(e);
         CK(cudaStreamSynchronize(ctx->stream));
     }
     svmb200_default_params(&ctx->params);
@@ -885,7 +869,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     const int pitch4 = ctx->pitch4;
     if (int rc = ensure_model(ctx)) return rc;
 
-    float *Xq = nullptr;
+    void *Xq = nullptr;
     double *dscores = nullptr;
     int *dy = nullptr, *dcorrect = nullptr;
     CK(cudaMalloc(&Xq, (size_t)m * pitch4 * 16));
@@ -895,7 +879,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     int rc = ingest<T>(ctx, X, m, false, scale, Xq);
     cudaError_t e = cudaSuccess;
     if (!rc) {
-        e = launch_decision_any(q_for_pitch(pitch4), ctx->params.accum_chunk, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv,
+        e = launch_decision_any(KernelKey{ctx->x_f64, q_for_pitch(pitch4, ctx->x_f64), ctx->params.accum_chunk, 0}, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv,
                                 pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores, ctx->stream);
         ctx->launches += 1;
     }
@@ -967,13 +951,8 @@ int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_
     if (int rc = ensure_norms(ctx, CH)) return rc;
     if (int rc = ensure_scratch(ctx, (size_t)ctx->n * sizeof(double))) return rc;
     double *out = static_cast<double *>(ctx->scratch);
-    const int Q = q_for_pitch(ctx->pitch4);
-    cudaError_t e;
-    switch (CH) {
-    case 1: e = launch_krow_q<1>(Q, ctx->X, ctx->sqn, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
-    case 2: e = launch_krow_q<2>(Q, ctx->X, ctx->sqn, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
-    default: e = launch_krow_q<4>(Q, ctx->X, ctx->sqn, ctx->n, ctx->pitch4, i, gamma, out, ctx->stream); break;
-    }
+    cudaError_t e = launch_krow_any(KernelKey{ctx->x_f64, q_for_pitch(ctx->pitch4, ctx->x_f64), CH, 0}, ctx->X, ctx->x_f64 ? nullptr : ctx->sqn,
+                                    ctx->n, ctx->pitch4, i, gamma, out, ctx->stream);
     ctx->launches += 1;
     CK(e);
     CK(cudaMemcpyAsync(row, out, (size_t)ctx->n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1010,6 +989,13 @@ int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs)
     if (!ctx || !Xs) return SVMB200_EINVAL;
     if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set");
     CK(cudaSetDevice(ctx->device));
+    if (ctx->x_f64) {       // exact storage: hand back the rows rounded to fp32
+        std::vector<double> tmp((size_t)ctx->n * ctx->d);
+        CK(cudaMemcpy2D(tmp.data(), (size_t)ctx->d * sizeof(double), ctx->X, (size_t)ctx->pitch4 * 16, (size_t)ctx->d * sizeof(double),
+                        (size_t)ctx->n, cudaMemcpyDeviceToHost));
+        for (size_t k = 0; k < tmp.size(); ++k) Xs[k] = (float)tmp[k];
+        return SVMB200_OK;
+    }
     CK(cudaMemcpy2D(Xs, (size_t)ctx->d * sizeof(float), ctx->X, (size_t)ctx->pitch4 * 16, (size_t)ctx->d * sizeof(float),
                     (size_t)ctx->n, cudaMemcpyDeviceToHost));
     return SVMB200_OK;

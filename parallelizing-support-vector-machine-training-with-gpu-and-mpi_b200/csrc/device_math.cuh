@@ -110,6 +110,34 @@ __device__ __forceinline__ double sqdist_from_dot(double na, double nb, double a
     return s < 0.0 ? 0.0 : s;
 }
 
+// ---- the two storage precisions of X.  A row is a sequence of 16-byte groups either way: four fp32 values
+// (the fast path: norm + dot product) or two FP64 values (the exact path: squared differences in FP64, the
+// reference's own formula, main3.cpp:97-100, summed per lane instead of sequentially).
+template <typename XT> struct RowVec;
+template <> struct RowVec<float> { using type = float4; };
+template <> struct RowVec<double> { using type = double2; };
+template <typename V> __device__ __forceinline__ V vec_zero();
+template <> __device__ __forceinline__ float4 vec_zero<float4>() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+template <> __device__ __forceinline__ double2 vec_zero<double2>() { return make_double2(0.0, 0.0); }
+
+template <int CH>
+__device__ __forceinline__ void accum_pair(const float4 &v, const float4 &p, double &acc) { accum_dot<CH>(v, p, acc); }
+template <int CH>
+__device__ __forceinline__ void accum_pair(const double2 &v, const double2 &p, double &acc)
+{
+    const double d0 = v.x - p.x;
+    acc = fma(d0, d0, acc);
+    const double d1 = v.y - p.y;
+    acc = fma(d1, d1, acc);
+}
+// squared distance from what accum_pair summed: fp32 rows give the dot product (norms needed), FP64 rows the distance itself
+template <typename XT>
+__device__ __forceinline__ double dist2(double na, double nb, double s)
+{
+    if (sizeof(XT) == 4) return sqdist_from_dot(na, nb, s);
+    return s;
+}
+
 // (value, lowest index) ordering of calc_i_high / calc_i_low (code/main3.cpp:113-120,132-139):
 // the reference scans ascending with a strict compare, so among equal f the lowest index wins.
 __device__ __forceinline__ bool better_min(double fa, int ia, double fb, int ib)

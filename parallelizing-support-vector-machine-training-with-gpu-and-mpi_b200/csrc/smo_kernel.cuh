@@ -43,7 +43,7 @@ struct SmoResult {
 };
 
 struct SmoArgs {
-    const float *X;        // [n][pitch4*4] fp32, zero padded
+    const void *X;         // [n][pitch4] 16-byte groups: 4 fp32 or 2 FP64 values each, zero padded
     const double *sqn;     // [n] squared norms |x_j|^2 (dot product of the row with itself)
     const int *y;          // +-1
     double *f;
@@ -55,7 +55,7 @@ struct SmoArgs {
     int *trace;            // [trace_cap][2]
     SmoResult *result;
     long long n;
-    int pitch4;            // float4 groups per row
+    int pitch4;            // 16-byte groups per row
     int kslots;            // ring depth per warp (2..SMO_KSLOTS_MAX), chosen so the ring fits in shared memory
     int cache_cap;
     int trace_cap;
@@ -78,14 +78,14 @@ struct SmoArgs {
 };
 
 // ------------------------------------------------------------------------------------------
-template <int Q>
+template <typename Vec, int Q>
 struct Pivots {
-    float4 h[Q];
-    float4 l[Q];
+    Vec h[Q];
+    Vec l[Q];
 };
 
-template <int Q, int CH>
-__device__ __forceinline__ void row_dot2(const float4 *__restrict__ row, const Pivots<Q> &pv, int pitch4, int lane,
+template <typename Vec, int Q, int CH>
+__device__ __forceinline__ void row_dot2(const Vec *__restrict__ row, const Pivots<Vec, Q> &pv, int pitch4, int lane,
                                          double &dh, double &dl)
 {
     double ah = 0.0, al = 0.0;
@@ -93,9 +93,9 @@ __device__ __forceinline__ void row_dot2(const float4 *__restrict__ row, const P
     for (int i = 0; i < Q; ++i) {
         const int q = i * 32 + lane;
         if (q < pitch4) {
-            const float4 v = row[q];
-            accum_dot<CH>(v, pv.h[i], ah);
-            accum_dot<CH>(v, pv.l[i], al);
+            const Vec v = row[q];
+            accum_pair<CH>(v, pv.h[i], ah);
+            accum_pair<CH>(v, pv.l[i], al);
         }
     }
     warp_sum_butterfly2(ah, al, lane);
@@ -368,13 +368,15 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
 }
 
 // ------------------------------------------------------------------------------------------
-template <int Q, int CH, int THREADS>
+template <typename XT, int Q, int CH, int THREADS>
 __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid_constant__ SmoArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int G = gridDim.x;
     constexpr int WARPS = THREADS / 32;
+    using Vec = typename RowVec<XT>::type;
+    const unsigned char *Xb = static_cast<const unsigned char *>(a.X);
     const int row_bytes = a.pitch4 * 16;
     // shared-memory carve-up: [warps][slots] rows | mbarriers | Shared
     unsigned char *slots = smem_raw;
@@ -410,12 +412,12 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     auto issue_into = [&](int s) {       // called by the whole warp (state stays warp-uniform); lane 0 issues
         if (lane == 0) {
             mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
-            bulk_g2s(my_slots + (size_t)s * row_bytes, a.X + (size_t)(w0 + pf_row) * a.pitch4 * 4, (unsigned)row_bytes,
+            bulk_g2s(my_slots + (size_t)s * row_bytes, Xb + (size_t)(w0 + pf_row) * row_bytes, (unsigned)row_bytes,
                      &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
             if (ahead > 0) {             // and the row `ahead` places further on goes from HBM into L2
                 int r = pf_row + ahead;
                 if (r >= m) r -= m;
-                bulk_prefetch_l2(a.X + (size_t)(w0 + r) * a.pitch4 * 4, (unsigned)row_bytes, a.policy_stream);
+                bulk_prefetch_l2(Xb + (size_t)(w0 + r) * row_bytes, (unsigned)row_bytes, a.policy_stream);
             }
         }
         if (++pf_row == m) pf_row = 0;
@@ -423,7 +425,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     if (m > 0) {
         if (lane == 0)
             for (int r = KS; r < KS + ahead; ++r)
-                bulk_prefetch_l2(a.X + (size_t)(w0 + r) * a.pitch4 * 4, (unsigned)row_bytes, a.policy_stream);
+                bulk_prefetch_l2(Xb + (size_t)(w0 + r) * row_bytes, (unsigned)row_bytes, a.policy_stream);
         for (int s = 0; s < KS; ++s) issue_into(s);
     }
 
@@ -463,26 +465,25 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         const bool use_cache = hit_h && hit_l;
 
         // K12 = K(i_high, i_low)  (main3.cpp:241)
-        Pivots<Q> pv;
+        Pivots<Vec, Q> pv;
         double K12, n_h = 0.0, n_l = 0.0;
         if (!use_cache) {
-            const float4 *xh = reinterpret_cast<const float4 *>(a.X) + (size_t)i_high * a.pitch4;
-            const float4 *xl = reinterpret_cast<const float4 *>(a.X) + (size_t)i_low * a.pitch4;
+            const Vec *xh = reinterpret_cast<const Vec *>(a.X) + (size_t)i_high * a.pitch4;
+            const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)i_low * a.pitch4;
 #pragma unroll
             for (int i = 0; i < Q; ++i) {
                 const int q = i * 32 + lane;
-                pv.h[i] = q < a.pitch4 ? __ldg(xh + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-                pv.l[i] = q < a.pitch4 ? __ldg(xl + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                pv.h[i] = q < a.pitch4 ? __ldg(xh + q) : vec_zero<Vec>();
+                pv.l[i] = q < a.pitch4 ? __ldg(xl + q) : vec_zero<Vec>();
             }
-            n_h = a.sqn[i_high];
-            n_l = a.sqn[i_low];
+            if (sizeof(XT) == 4) { n_h = a.sqn[i_high]; n_l = a.sqn[i_low]; }
             SVM_STAMP(15);
             double acc = 0.0;
 #pragma unroll
             for (int i = 0; i < Q; ++i)
-                if (i * 32 + lane < a.pitch4) accum_dot<CH>(pv.l[i], pv.h[i], acc);
+                if (i * 32 + lane < a.pitch4) accum_pair<CH>(pv.l[i], pv.h[i], acc);
             acc = warp_sum_butterfly(acc);
-            K12 = svm_exp(-a.gamma * sqdist_from_dot(n_h, n_l, acc));
+            K12 = svm_exp(-a.gamma * dist2<XT>(n_h, n_l, acc));
         } else if (i_low >= a.row_begin && i_low < a.row_end) {
             // the one read of a value another CTA wrote: column i_low of the cached row was stored by the CTA that
             // owns row i_low, at least one exchange ago (its __threadfence below, this CTA's fence after the counter
@@ -491,16 +492,16 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         } else {
             // row sharding: column i_low of the cached rows lives on the GPU that owns row i_low; X is
             // replicated, so form K12 here the way that GPU formed it (same code, same bits)
-            const float4 *xh = reinterpret_cast<const float4 *>(a.X) + (size_t)i_high * a.pitch4;
-            const float4 *xl = reinterpret_cast<const float4 *>(a.X) + (size_t)i_low * a.pitch4;
+            const Vec *xh = reinterpret_cast<const Vec *>(a.X) + (size_t)i_high * a.pitch4;
+            const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)i_low * a.pitch4;
             double acc = 0.0;
 #pragma unroll
             for (int i = 0; i < Q; ++i) {
                 const int q = i * 32 + lane;
-                if (q < a.pitch4) accum_dot<CH>(__ldg(xl + q), __ldg(xh + q), acc);
+                if (q < a.pitch4) accum_pair<CH>(__ldg(xl + q), __ldg(xh + q), acc);
             }
             acc = warp_sum_butterfly(acc);
-            K12 = svm_exp(-a.gamma * sqdist_from_dot(a.sqn[i_high], a.sqn[i_low], acc));
+            K12 = svm_exp(-a.gamma * dist2<XT>(sizeof(XT) == 4 ? a.sqn[i_high] : 0.0, sizeof(XT) == 4 ? a.sqn[i_low] : 0.0, acc));
         }
 
         // scalar update, main3.cpp:235-270, operation for operation
@@ -558,12 +559,12 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 int yj = 0;
                 long long qj = -1;
                 double nj = 0.0;
-                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; nj = a.sqn[j]; if (a.cacheq) qj = a.cacheq[j]; }
+                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; if (sizeof(XT) == 4) nj = a.sqn[j]; if (a.cacheq) qj = a.cacheq[j]; }
                 double my_dh = 0.0, my_dl = 0.0;
                 for (int t = 0; t < cnt; ++t) {
                     mbar_wait(&my_bars[cslot], cphase);
                     double dh, dl;
-                    row_dot2<Q, CH>(reinterpret_cast<const float4 *>(my_slots + (size_t)cslot * row_bytes), pv, a.pitch4, lane, dh, dl);
+                    row_dot2<Vec, Q, CH>(reinterpret_cast<const Vec *>(my_slots + (size_t)cslot * row_bytes), pv, a.pitch4, lane, dh, dl);
                     if (lane == t) { my_dh = dh; my_dl = dl; }
                     // the slot is free again: request the next row of the ring into it
                     __syncwarp();
@@ -572,8 +573,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
                 }
                 if (lane < cnt) {
-                    const double kh = svm_exp(-a.gamma * sqdist_from_dot(n_h, nj, my_dh));
-                    const double kl = svm_exp(-a.gamma * sqdist_from_dot(n_l, nj, my_dl));
+                    const double kh = svm_exp(-a.gamma * dist2<XT>(n_h, nj, my_dh));
+                    const double kl = svm_exp(-a.gamma * dist2<XT>(n_l, nj, my_dl));
                     fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
                     a.f[j] = fj;
                     if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
@@ -589,7 +590,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 // the CTAs are in the record exchange
                 int r = pf_row;
                 for (int k = 0; k < a.l2_burst; ++k) {
-                    bulk_prefetch_l2(a.X + (size_t)(w0 + r) * a.pitch4 * 4, (unsigned)row_bytes, a.policy_stream);
+                    bulk_prefetch_l2(Xb + (size_t)(w0 + r) * row_bytes, (unsigned)row_bytes, a.policy_stream);
                     if (++r == m) r = 0;
                 }
             }

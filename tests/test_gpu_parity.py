@@ -268,3 +268,65 @@ def test_errors_are_reported(pkg):
     with pytest.raises(pkg.SvmB200Error, match="wss"):
         s.smo_train(wss=2)
     s.close()
+
+
+# ---- the exact path: FP64 storage of X (svmb200_set_exact) -------------------------------------------------
+
+@pytest.fixture()
+def exact_solver(pkg):
+    s = pkg.Solver(0)
+    s.set_exact(True)
+    yield s
+    s.close()
+
+
+def test_exact_path_bit_exact_vs_restated_arithmetic(exact_solver, O, dataset):
+    n = 700
+    X, _, y = dataset(n)
+    X = X.copy(); X[11] = X[5]
+    exact_solver.set_train_u8(X, y)
+    xs, mn, mx = O.scale(X)
+    for i in (0, 5, 699):
+        row = exact_solver.kernel_row(i)
+        exp = np.array([O.lib().oracle_device_kernel_f64(xs[i], xs[j], 784, 0.00125) for j in range(n)])
+        assert np.array_equal(row, exp)
+        ref = np.array([O.lib().oracle_kernel(xs[i], xs[j], 784, 0.00125) for j in range(n)])
+        assert np.max(np.abs(row - ref) / ref) < 1e-15            # vs the reference's sequential FP64 sum + libm exp
+    assert exact_solver.kernel_row(5)[11] == 1.0
+    out = exact_solver.smo_train(trace_cap=100000)
+    dev = O.smo_train(xs, y, arith=O.ARITH_DEVICE_F64, trace_cap=100000, want_f=True)
+    assert out["num_iter"] == dev["num_iter"]
+    assert np.array_equal(exact_solver.get_trace(100000), dev["trace"])
+    assert np.array_equal(out["alpha"], dev["alpha"]) and out["b"] == dev["b"]
+    assert np.array_equal(exact_solver.get_f(), dev["f"])
+    Xt, _, yt = dataset(200, split=1)
+    xt, _, _ = O.scale(Xt, mn, mx)
+    c_dev, s_dev = O.predict(xt, yt, xs, y, out["alpha"], out["b"], arith=O.ARITH_DEVICE_F64)
+    c_gpu, s_gpu = exact_solver.predict_u8(Xt, yt)
+    assert c_gpu == c_dev and np.array_equal(s_gpu, s_dev)
+    for cap in (-1, 16):                                           # row cache on the exact path
+        on = exact_solver.smo_train(cache_rows=cap)
+        assert np.array_equal(on["alpha"], out["alpha"]) and on["b"] == out["b"]
+    warm = exact_solver.smo_train(alpha0=out["alpha"])
+    assert warm["num_iter"] <= 3
+
+
+@pytest.mark.parametrize("n", [256, 2000, 10000])
+def test_exact_path_walks_the_reference_pair_sequence(exact_solver, dataset, n):
+    """FP64 rows: the working-pair sequence IS the reference's (north_star), not just a prefix of it."""
+    g = golden(n)
+    X, _, y = dataset(n)
+    exact_solver.set_train_u8(X, y)
+    out = exact_solver.smo_train(trace_cap=4096, cache_rows=-1)
+    assert out["num_iter"] == int(g["num_iter"])
+    tr = exact_solver.get_trace(4096)
+    assert np.array_equal(tr, g["trace"][:len(tr)])
+    assert (out["i_high"], out["i_low"]) == (int(g["i_high"]), int(g["i_low"]))
+    assert np.array_equal(exact_solver.sv_ids(), g["sv_ids"])
+    assert abs(out["b"] - float(g["b"])) <= 1e-12 * max(1.0, abs(float(g["b"])))
+    assert np.max(np.abs(out["alpha"][g["sv_ids"]] - g["sv_alpha"]) / g["sv_alpha"]) < 1e-9
+    m = int(g["m"])
+    Xt, _, yt = dataset(m, split=1)
+    correct, scores = exact_solver.predict_u8(Xt, yt)
+    assert correct == int(g["correct"])
+    assert np.allclose(scores[:256], g["scores_head"][:min(256, m)], rtol=0, atol=1e-11)
