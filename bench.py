@@ -250,6 +250,32 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         strong = {"rows": args.n, "us_per_iter": 1e3 * float(t.item()) / args.steps, "iters_per_sec": args.steps / (float(t.item()) / 1e3)}
 
+    # ---- the exact path (FP64 rows, svmb200_set_exact): same problem, the reference's own pair sequence
+    exact = None
+    if world == 1 and not args.no_exact:
+        es = pkg.Solver(local_rank)
+        es.set_exact(True)
+        es.set_train_u8(X, y)
+        for _ in range(3):
+            es.smo_train(max_iter=50, cache_rows=0)
+        ms = [es.smo_train(max_iter=args.steps, cache_rows=0)["smo_ms"] for _ in range(3)]
+        t0 = time.perf_counter()
+        es.set_train_u8(X, y)
+        full = es.smo_train(cache_rows=-1, trace_cap=4096)
+        secs = time.perf_counter() - t0
+        exact = {"us_per_iter_cache_off": 1e3 * float(np.median(ms)) / args.steps, "bytes_per_iteration": n * ((D + 1) // 2) * 16,
+                 "train_secs_cache_on": secs, "iterations": full["num_iter"] - 1, "n_sv": full["n_sv"], "b": full["b"]}
+        exact["GBps"] = exact["bytes_per_iteration"] / exact["us_per_iter_cache_off"] / 1e3
+        gpath = os.path.join(ROOT, "tests", "golden", f"golden_n{n}.npz")
+        if os.path.exists(gpath):
+            g = np.load(gpath)
+            tr = es.get_trace(4096)
+            exact.update({"iterations_reference": int(g["num_iter"]) - 1, "sv_set_equals_reference": bool(np.array_equal(es.sv_ids(), g["sv_ids"])),
+                          "first_4096_pairs_equal_reference": bool(np.array_equal(tr, g["trace"][:len(tr)])),
+                          "b_abs_err": abs(full["b"] - float(g["b"])),
+                          "alpha_max_rel_err": float(np.max(np.abs(full["alpha"][g["sv_ids"]] - g["sv_alpha"]) / g["sv_alpha"]))})
+        es.close()
+
     peak, peak_src = measured_peak()
     row_bytes = ((D + 3) // 4) * 16
     alg_bytes = args.n * row_bytes                                # per GPU per iteration: X once
@@ -303,7 +329,7 @@ def run_ours(args):
                         "what": "whole job from host buffers through the C ABI: svmb200_set_train_u8 (H2D + min/max + scale) + "
                                 "svmb200_smo_train to convergence (row cache off) + alpha D2H; value = N * iterations / wall seconds"},
                 "gpu_launches": out["launches"], "clocks": clocks, "wall_s_timed_call": wall,
-                "train": e2e_runs, "strong_scaling_60k": strong}
+                "train": e2e_runs, "strong_scaling_60k": strong, "exact_path_fp64_rows": exact}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -322,6 +348,7 @@ def main():
     ap.add_argument("--n", type=int, default=N_ROWS)
     ap.add_argument("--cpu-iters", type=int, default=150)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-exact", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
