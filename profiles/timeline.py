@@ -45,3 +45,11 @@ if k > 110:
         nxt_top = (g[it + 1, :, 0] - t0) / 1e3
         print(f"  iter {100 + it}: loop-top spread {top.max():.2f} us | pass end min/median/max {pe.min():.2f}/{np.median(pe):.2f}/{pe.max():.2f} us"
               f" | pass len min/med/max {(pe - sc).min():.2f}/{np.median(pe - sc):.2f}/{(pe - sc).max():.2f} | next loop top {nxt_top.min():.2f}..{nxt_top.max():.2f}")
+    # is the arrival skew systematic?  per-CTA pass-end offset (relative to the iteration's median), iterations 101..106
+    offs = np.array([(g[it, :, 2] - np.median(g[it, :, 2])) / 1e3 for it in range(1, 7)])
+    print("  per-CTA pass-end offset: mean over iterations min/max %.2f/%.2f us, std across iterations (median CTA) %.2f us" %
+          (offs.mean(0).min(), offs.mean(0).max(), np.median(offs.std(0))))
+    c = np.corrcoef(offs)
+    print("  correlation of the offset vector between iterations: mean off-diagonal %.2f" % ((c.sum() - np.trace(c)) / (c.size - len(c))))
+    late = np.argsort(-offs.mean(0))[:8]
+    print("  latest CTAs:", [(int(b), round(float(offs.mean(0)[b]), 2)) for b in late])

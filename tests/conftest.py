@@ -14,7 +14,9 @@ def pytest_configure(config):
 
 @pytest.fixture(scope="session")
 def pkg():
-    return entry.load_package()
+    mod = entry.load_package()
+    mod.build_library()          # no-op when libsvmb200.so is newer than its sources (nvcc cross-compiles without a GPU)
+    return mod
 
 
 @pytest.fixture(scope="session")

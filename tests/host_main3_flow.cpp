@@ -1,53 +1,43 @@
-// The reference's main() (code/main3.cpp:306-417), statement for statement, compiled against the svmb200
-// host layer instead of the reference's own function bodies.  The dataset name is argv[1] instead of the
-// hard-coded "mnist3" (main3.cpp:311); everything else is the reference's sequence.  Prints SV ids too.
-#include <chrono>
-#include <iomanip>
+// Drop-in check for the C++ host layer: the call sequence of the reference's serial program (read CSV, per-feature
+// min/max, scale, SMO_train, support-vector indices, scale the test set with the train statistics, predict;
+// code/main3.cpp:306-405) written against svmb200's reference-named functions.  argv[1] is the dataset prefix.
+#include <cstdio>
 #include <iostream>
 #include "svmb200_host.hpp"
-using namespace std;
-using namespace std::chrono;
-using namespace svmb200;
 
 int main(int argc, char **argv)
 {
-    string dataset = argc > 1 ? argv[1] : "mnist3";
-    string train_file = dataset + "_train_data.csv";
-    vector<double> x_train;
-    vector<int> y_train;
-    size_t n_features;
-    read_CSV(train_file, x_train, y_train, n_features);
-    size_t n = x_train.size() / n_features;
-    cout << "n = " << n << endl;
-    cout << "n_features = " << n_features << endl;
-    if (n == 0) { cerr << "Error: No data read from file." << endl; return 1; }
-    vector<double> min_val(n_features, 0.0);
-    vector<double> max_val(n_features, 0.0);
-    find_min_max(x_train, min_val, max_val, n, n_features);
-    scale_features(x_train, min_val, max_val, n, n_features);
-    double C = 10.0;
-    vector<double> alpha(n, 0.0);
-    double b;
-    SMO_train(x_train, y_train, n_features, alpha, b, C);
-    string test_file = dataset + "_test_data.csv";
-    vector<double> x_test;
-    vector<int> y_test;
-    read_CSV(test_file, x_test, y_test, n_features);
-    size_t m = x_test.size() / n_features;
-    scale_features(x_test, min_val, max_val, m, n_features);
-    double tol = 1e-8;
-    vector<int> sv_idx = get_SV_indices(alpha, tol);
-    int sv_count = (int)sv_idx.size();
-    cout << "Final SV count = " << sv_count << "\n";
-    int correct = predict(x_test, y_test, n_features);
-    double accuracy = double(correct) / double(m);
-    cout << "Test accuracy = " << std::fixed << std::setprecision(15) << accuracy << " (" << correct << "/" << m << ")\n";
-    cout << "SV ids:";
-    for (int i : sv_idx) cout << " " << i;
-    cout << "\n";
-    // warm restart as the Cascade stages do (mpi_svm_main2.cpp:507): init = false keeps alpha
-    double b2;
-    SMO_train(x_train, y_train, n_features, alpha, b2, C, false);
-    cout << "warm restart b = " << std::fixed << std::setprecision(15) << b2 << endl;
+    namespace sv = svmb200;
+    const std::string prefix = argc > 1 ? argv[1] : "mnist3";
+    std::vector<double> xtr, xte;
+    std::vector<int> ytr, yte;
+    size_t d = 0;
+    sv::read_CSV(prefix + "_train_data.csv", xtr, ytr, d);
+    const size_t n = d ? xtr.size() / d : 0;
+    std::printf("n = %zu\nn_features = %zu\n", n, d);
+    if (!n) return 1;
+
+    std::vector<double> lo, hi;
+    sv::find_min_max(xtr, lo, hi, n, d);
+    sv::scale_features(xtr, lo, hi, n, d);
+
+    std::vector<double> alpha;
+    double b = 0.0;
+    sv::SMO_train(xtr, ytr, d, alpha, b, 10.0);                 // prints iterations and b as the reference does
+    const std::vector<int> svs = sv::get_SV_indices(alpha, 1e-8);
+    std::printf("Final SV count = %zu\n", svs.size());
+
+    sv::read_CSV(prefix + "_test_data.csv", xte, yte, d);
+    const size_t m = xte.size() / d;
+    sv::scale_features(xte, lo, hi, m, d);                       // train statistics, main3.cpp:355
+    const int correct = sv::predict(xte, yte, d);
+    std::printf("Test accuracy = %.15f (%d/%zu)\n", double(correct) / double(m), correct, m);
+    std::printf("SV ids:");
+    for (int i : svs) std::printf(" %d", i);
+    std::printf("\n");
+
+    double b2 = 0.0;                                             // the Cascade stages restart from alpha: init = false
+    sv::SMO_train(xtr, ytr, d, alpha, b2, 10.0, false);
+    std::printf("warm restart b = %.15f\n", b2);
     return 0;
 }
