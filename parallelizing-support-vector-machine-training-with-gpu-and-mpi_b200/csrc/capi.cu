@@ -466,7 +466,7 @@ static int ensure_norms(svmb200_ctx *ctx, int CH)
     return 0;
 }
 
-static const int SMO_DEFAULT_THREADS_Q7 = 512;
+static const int SMO_DEFAULT_THREADS_Q7 = 384;   // 12 warps, 164 registers each, no spills: 33.4 us/iteration at 60k against 35.4 with 512 threads
 static const int DEFAULT_CHUNK = 4;   // fp32 storage of X dominates the error of K for every chunk (DESIGN.md "Numerics")
 
 static int resolve_chunk(int c)
@@ -526,9 +526,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         }
     }
     const int warps = threads / 32;
-    // two rows per warp in flight (16 warps x 2 x 3136 B = 98 KB per SM) already saturate HBM; deeper
-    // rings only lengthen the queues the record exchange has to wait behind (profiles/r1_notes.md)
-    int kslots = 2;
+    // ring depth per warp: 4 rows with the 12-warp CTA of the MNIST shape (12 x 4 x 3136 B = 147 KB per SM in flight), 2 elsewhere
+    // (with 16 warps two rows per warp already saturate HBM and deeper rings only lengthen the queues the exchange waits behind)
+    int kslots = (Q == 7 && !ctx->x_f64) ? 4 : 2;
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
     while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps) > (size_t)ctx->max_smem_optin) --kslots;
     const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps);
