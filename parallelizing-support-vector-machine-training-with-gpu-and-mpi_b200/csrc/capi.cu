@@ -54,7 +54,7 @@ struct svmb200_ctx {
     double *f = nullptr, *alpha = nullptr;
     long long *cacheq = nullptr;
     double *cacheK = nullptr;
-    long long cacheK_rows = 0;
+    size_t cacheK_elems = 0;
     Rec *rec = nullptr;
     int rec_blocks = 0;
     SmoResult *result = nullptr;
@@ -248,7 +248,7 @@ static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool comput
 {
     const int d = ctx->d, pitch4 = ctx->pitch4;
     const size_t raw_bytes = (size_t)rows * d * sizeof(T);
-    const int parts = (int)std::min<long long>(ctx->num_sms * 4, (rows + 63) / 64);
+    const int parts = (int)std::min<long long>(ctx->num_sms, (rows + 63) / 64);
     const size_t part_bytes = compute_stats ? (size_t)2 * parts * d * sizeof(double) : 0;
     const size_t raw_off = (part_bytes + 255) & ~(size_t)255;
     if (int rc = ensure_scratch(ctx, raw_off + raw_bytes)) return rc;
@@ -543,11 +543,11 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         cache_cap = (int)std::min<long long>(n, (long long)(budget / ((size_t)n * sizeof(double))));
     }
     if (cache_cap == 1) cache_cap = 2;
-    if (cache_cap > 0 && (long long)cache_cap != ctx->cacheK_rows) {
+    if (cache_cap > 0 && (size_t)cache_cap * n > ctx->cacheK_elems) {     // sized in elements: the same capacity needs more room when n grows
         if (dev_free(ctx, ctx->cacheK)) return SVMB200_ECUDA;
-        ctx->cacheK_rows = 0;
+        ctx->cacheK_elems = 0;
         CK(cudaMalloc(&ctx->cacheK, (size_t)cache_cap * n * sizeof(double)));
-        ctx->cacheK_rows = cache_cap;
+        ctx->cacheK_elems = (size_t)cache_cap * n;
     }
 
     if (grid > ctx->rec_blocks) {

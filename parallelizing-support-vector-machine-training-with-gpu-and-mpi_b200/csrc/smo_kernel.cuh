@@ -464,6 +464,18 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         }
         const bool use_cache = hit_h && hit_l;
 
+        // cached iteration: this thread's first row of the pass is requested now, so that its loads and the K12 load
+        // below travel together instead of one L2 round trip after the other
+        const long long pj = r0 + threadIdx.x;
+        double p_f = 0.0, p_a = 0.0, p_kh = 0.0, p_kl = 0.0;
+        int p_y = 0;
+        long long p_q = -1;
+        if (use_cache && pj < r1) {
+            p_f = a.f[pj]; p_a = a.alpha[pj]; p_y = a.y[pj]; p_q = a.cacheq[pj];
+            p_kh = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + pj];
+            p_kl = a.cacheK[(size_t)(q_l % a.cache_cap) * a.n + pj];
+        }
+
         // K12 = K(i_high, i_low)  (main3.cpp:241)
         Pivots<Vec, Q> pv;
         double K12, n_h = 0.0, n_l = 0.0;
@@ -599,11 +611,13 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             ++cache_hits;
             const double *kh_row = a.cacheK + (size_t)slot_h * a.n;
             const double *kl_row = a.cacheK + (size_t)slot_l * a.n;
-            for (long long j = r0 + threadIdx.x; j < r1; j += THREADS) {
-                double fj = a.f[j], aj = a.alpha[j];
-                const int yj = a.y[j];
-                const long long qj = a.cacheq[j];
-                fj = fj + (c_h * kh_row[j] + c_l * kl_row[j]);
+            for (long long j = pj; j < r1; j += THREADS) {
+                const bool first = j == pj;
+                double fj = first ? p_f : a.f[j], aj = first ? p_a : a.alpha[j];
+                const int yj = first ? p_y : a.y[j];
+                const long long qj = first ? p_q : a.cacheq[j];
+                const double khj = first ? p_kh : kh_row[j], klj = first ? p_kl : kl_row[j];
+                fj = fj + (c_h * khj + c_l * klj);
                 a.f[j] = fj;
                 if (j == i_high) { aj = na_h; a.alpha[j] = aj; }
                 if (j == i_low) { aj = na_l; a.alpha[j] = aj; }

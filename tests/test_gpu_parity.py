@@ -154,6 +154,16 @@ def test_cache_on_equals_cache_off(solver, O, dataset):
         assert np.array_equal(on["alpha"], off["alpha"]) and on["b"] == off["b"] and on["num_iter"] == off["num_iter"], cap
 
 
+def test_same_cache_capacity_on_a_bigger_problem(solver, dataset):
+    """An explicit cache capacity kept across uploads of growing size (the cache is sized in elements, not rows)."""
+    for n in (200, 1200):
+        X, _, y = dataset(n)
+        solver.set_train_u8(X, y)
+        off = solver.smo_train(cache_rows=0)
+        on = solver.smo_train(cache_rows=48)
+        assert np.array_equal(on["alpha"], off["alpha"]) and on["b"] == off["b"]
+
+
 def test_warm_start_matches_oracle(solver, O, dataset):
     """init=false: alpha in/out, f rebuilt from alpha (mpi_svm_main2.cpp:167-183)."""
     n = 800
