@@ -164,7 +164,17 @@ int svmb200_shard_setup(svmb200_ctx *ctx, int32_t rank, int32_t world, void *han
 int svmb200_shard_connect(svmb200_ctx *ctx, int32_t world, const void *handles /* world x 64 bytes */);
 int svmb200_set_model(svmb200_ctx *ctx, const double *alpha, double b);
 
+/* ---- the decision function on the tensor cores (tcgen05 / TMEM, TF32x3): svmb200_predict_* on fp32 storage first
+ * forms all scores with the tensor cores (error up to ~1e-3: fp32 accumulation of three tf32 products), then
+ * re-evaluates every row with |score| < recheck_threshold by the exact kernel, so predicted labels and accuracy are
+ * those of the exact path; returned scores are exact for the re-evaluated rows and approximate for the others.
+ * Off by default.  A threshold of 0.05 is ample for C = 10. */
+int svmb200_set_tensor_cores(svmb200_ctx *ctx, int32_t enable, double recheck_threshold);
+
 /* ---- introspection used by the parity tests ---- */
+/* raw tensor-core dot products of the first min(n,128) training rows against themselves (128 x 128 floats, dots may
+ * be NULL), and the number of rows the last svmb200_predict_* re-evaluated exactly */
+int svmb200_debug_tc_dots(svmb200_ctx *ctx, float *dots, int64_t *rechecked);
 /* (i_high, i_low) of the first min(cap, recorded) iterations that reached the update */
 int svmb200_get_trace(svmb200_ctx *ctx, int32_t *pairs, int32_t cap, int32_t *count);
 /* final error vector f (n doubles) */

@@ -85,6 +85,8 @@ def load_library():
     L.svmb200_kernel_row.argtypes = [vp, i64, dbl, i32, vp]
     L.svmb200_select_pair.argtypes = [vp, vp, vp, vp, i64, dbl, dbl, C.POINTER(i64), C.POINTER(i64)]
     L.svmb200_get_x_scaled.argtypes = [vp, vp]
+    L.svmb200_set_tensor_cores.argtypes = [vp, i32, dbl]
+    L.svmb200_debug_tc_dots.argtypes = [vp, vp, C.POINTER(i64)]
     L.svmb200_save_model.argtypes = [vp, C.c_char_p]
     L.svmb200_load_model.argtypes = [vp, C.c_char_p]
     L.svmb200_shard_setup.argtypes = [vp, i32, i32, vp]
@@ -218,6 +220,20 @@ class Solver:
 
     def predict_scaled(self, Xs, y_test=None, ge_zero=False):
         return self._predict(self.L.svmb200_predict_scaled_f64, Xs, np.float64, y_test, ge_zero)
+
+    def set_tensor_cores(self, enable: bool, recheck_threshold: float = 0.05):
+        self._ck(self.L.svmb200_set_tensor_cores(self.h, 1 if enable else 0, recheck_threshold), "set_tensor_cores")
+
+    def tc_dots(self):
+        dots = np.zeros((128, 128), dtype=np.float32)
+        r = C.c_int64()
+        self._ck(self.L.svmb200_debug_tc_dots(self.h, _ptr(dots), C.byref(r)), "debug_tc_dots")
+        return dots
+
+    def tc_rechecked(self) -> int:
+        r = C.c_int64()
+        self._ck(self.L.svmb200_debug_tc_dots(self.h, None, C.byref(r)), "debug_tc_dots")
+        return r.value
 
     def save_model(self, path: str):
         self._ck(self.L.svmb200_save_model(self.h, path.encode()), "save_model")

@@ -13,6 +13,7 @@
 
 #include "aux_kernels.cuh"
 #include "smo_kernel.cuh"
+#include "tc_decision.cuh"
 
 using namespace svm;
 
@@ -74,6 +75,11 @@ struct svmb200_ctx {
     int model_nsv = 0;
     std::vector<int> model_y;   // labels of the support vectors (kept for svmb200_save_model)
     int sv_alloc = 0;
+
+    // tensor-core decision function (svmb200_set_tensor_cores)
+    bool tc_predict = false;
+    double tc_threshold = 0.05;
+    long long tc_rechecked = 0;
 
     // row sharding over several GPUs (one process per GPU; see svmb200_shard_*)
     int shard_rank = 0, shard_world = 1, shard_epoch = 0;
@@ -827,6 +833,42 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
     return SVMB200_OK;
 }
 
+// ---- tensor-core decision function
+extern "C" int svmb200_set_tensor_cores(svmb200_ctx *ctx, int32_t enable, double recheck_threshold)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (enable && !(recheck_threshold > 0.0)) FAIL(SVMB200_EINVAL, "recheck_threshold must be positive");
+    ctx->tc_predict = enable != 0;
+    if (enable) ctx->tc_threshold = recheck_threshold;
+    return SVMB200_OK;
+}
+
+// introspection: the raw tensor-core dot products of the first 128 training rows against themselves (128 x 128),
+// and how many rows the last svmb200_predict_* sent to the exact kernel
+extern "C" int svmb200_debug_tc_dots(svmb200_ctx *ctx, float *dots, int64_t *rechecked)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (rechecked) *rechecked = ctx->tc_rechecked;
+    if (!dots) return SVMB200_OK;
+    if (!ctx->have_train || ctx->x_f64) FAIL(SVMB200_ESTATE, "needs an fp32 training set");
+    CK(cudaSetDevice(ctx->device));
+    const long long rows = std::min<long long>(ctx->n, TC_M);
+    if (int rc = ensure_norms(ctx, DEFAULT_CHUNK)) return rc;
+    if (int rc = ensure_scratch(ctx, (size_t)TC_M * TC_N * sizeof(float) + (size_t)TC_M * 2 * sizeof(double))) return rc;
+    float *d_dots = static_cast<float *>(ctx->scratch);
+    double *coef = reinterpret_cast<double *>(d_dots + TC_M * TC_N), *out = coef + TC_M;
+    CK(cudaMemsetAsync(ctx->scratch, 0, (size_t)TC_M * TC_N * sizeof(float) + (size_t)TC_M * 2 * sizeof(double), ctx->stream));
+    CK(cudaFuncSetAttribute(decision_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_smem_bytes()));
+    decision_tc_kernel<<<1, TC_THREADS, decision_tc_smem_bytes(), ctx->stream>>>(static_cast<const float *>(ctx->X), ctx->sqn, rows,
+                                                                               static_cast<const float *>(ctx->X), ctx->sqn, coef, (int)rows,
+                                                                               ctx->pitch4 * 4, ctx->d, 0.0, 0.0, out, d_dots);
+    ctx->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dots, d_dots, (size_t)TC_M * TC_N * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SVMB200_OK;
+}
+
 extern "C" int svmb200_sv_ids(svmb200_ctx *ctx, int32_t *ids, int32_t cap, int32_t *count)
 {
     if (!ctx) return SVMB200_EINVAL;
@@ -878,8 +920,54 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     dcorrect = dy + m;
     int rc = ingest<T>(ctx, X, m, false, scale, Xq);
     cudaError_t e = cudaSuccess;
-    if (!rc) {
-        e = launch_decision_any(KernelKey{ctx->x_f64, q_for_pitch(pitch4, ctx->x_f64), ctx->params.accum_chunk, 0}, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv,
+    const KernelKey key{ctx->x_f64, q_for_pitch(pitch4, ctx->x_f64), ctx->params.accum_chunk, 0};
+    if (!rc && ctx->tc_predict && !ctx->x_f64 && ctx->model_nsv > 0) {
+        // tensor cores first (TF32x3, approximate), then the exact kernel for every row whose |score| is under the threshold
+        const int nsv = ctx->model_nsv;
+        double *qn = nullptr, *exact = nullptr;
+        int *list = nullptr;
+        float *Xu = nullptr;
+        e = cudaMalloc(&qn, (size_t)m * sizeof(double));
+        if (e == cudaSuccess) e = cudaMalloc(&list, ((size_t)m + 1) * sizeof(int));
+        if (e == cudaSuccess) e = launch_sqnorm_any(key, static_cast<const float *>(Xq), m, pitch4, qn, ctx->stream);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(decision_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_smem_bytes());
+        if (e == cudaSuccess) {
+            decision_tc_kernel<<<(unsigned)((m + TC_M - 1) / TC_M), TC_THREADS, decision_tc_smem_bytes(), ctx->stream>>>(
+                static_cast<const float *>(Xq), qn, m, static_cast<const float *>(ctx->svX), ctx->svn, ctx->svcoef, nsv, pitch4 * 4, ctx->d,
+                ctx->params.gamma, -ctx->b, dscores, nullptr);
+            e = cudaGetLastError();
+        }
+        int n_unc = 0;
+        if (e == cudaSuccess) e = cudaMemsetAsync(list + m, 0, sizeof(int), ctx->stream);
+        if (e == cudaSuccess) {
+            flag_uncertain_kernel<<<std::min<long long>((m + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(dscores, m, ctx->tc_threshold, list, list + m);
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&n_unc, list + m, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        ctx->launches += 3;
+        if (e == cudaSuccess && n_unc > 0) {
+            e = cudaMalloc(&Xu, (size_t)n_unc * pitch4 * 16);
+            if (e == cudaSuccess) e = cudaMalloc(&exact, (size_t)n_unc * sizeof(double));
+            if (e == cudaSuccess) {
+                const long long total = (long long)n_unc * pitch4;
+                gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+                    Xq, nullptr, pitch4, list, n_unc, Xu, qn /* norms unused by the exact kernel: scratch */);
+                e = cudaGetLastError();
+            }
+            if (e == cudaSuccess)
+                e = launch_decision_any(key, Xu, n_unc, ctx->svX, ctx->svn, ctx->svcoef, nsv, pitch4, ctx->params.gamma, -ctx->b, nullptr, exact, ctx->stream);
+            if (e == cudaSuccess) {
+                scatter_scores_kernel<<<(n_unc + 255) / 256, 256, 0, ctx->stream>>>(exact, list, n_unc, dscores);
+                e = cudaGetLastError();
+            }
+            ctx->launches += 3;
+        }
+        ctx->tc_rechecked = n_unc;
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(qn); cudaFree(list); cudaFree(Xu); cudaFree(exact);
+    } else if (!rc) {
+        e = launch_decision_any(key, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv,
                                 pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores, ctx->stream);
         ctx->launches += 1;
     }

@@ -1,0 +1,180 @@
+// tc_decision.cuh -- the batched decision function on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// The one GEMM-shaped piece of the path: scores = Q [m x d] . SV^T [d x n_sv] followed by exp and a weighted row
+// sum (code/main3.cpp:391-402 over all test rows at once; the reference GPU's predict kernel,
+// code/gpu_svm_main3.cu:277-293, walks ALL n training rows per test row in scalar FP64).
+//
+// One CTA owns 128 query rows (the M = 128 lanes of its TMEM accumulator) and walks the support vectors in tiles of
+// 128 (N = 128 accumulator columns).  Operands are staged in shared memory in the canonical K-major, no-swizzle
+// core-matrix layout and multiplied with tcgen05.mma kind::tf32; a tf32 operand keeps 10 mantissa bits, so every
+// fp32 value x is split into hi = x with the low 13 mantissa bits cleared and lo = x - hi (exact), and each
+// K step issues three MMAs: hi.hi + hi.lo + lo.hi ("TF32x3", fp32 accumulation in TMEM).  The epilogue reads the
+// accumulator with tcgen05.ld, forms K = exp(-gamma (|q|^2 + |s|^2 - 2 q.s)) and adds coef_k K to the row's FP64
+// sum.  Scores from this kernel carry an error of ~1e-3 at most (fp32 accumulation over d = 784 and 3 tf32
+// products); the caller re-evaluates every row whose |score| is below a threshold with the exact kernel
+// (decision_kernel), so the predicted labels -- and the accuracy -- are those of the exact path.
+#pragma once
+#include "device_math.cuh"
+
+namespace svm {
+
+constexpr int TC_M = 128;          // query rows per CTA = TMEM lanes
+constexpr int TC_N = 128;          // support vectors per tile = TMEM columns (fp32)
+constexpr int TC_KB = 32;          // K elements staged per step (8 core-matrix columns of 4 tf32 each)
+constexpr int TC_THREADS = 128;    // 4 warps: warp w reads TMEM lanes 32w .. 32w+31
+constexpr int TC_TILE_BYTES = TC_M * TC_KB * 4;   // 16 KB per operand tile
+
+// K-major, no swizzle: core matrix = 8 rows x 16 bytes (128 B, rows 16 B apart); core matrices adjacent in K are
+// 128 B apart (LBO), core matrices adjacent in M/N are 8 x 128 B = 1024 B apart (SBO)
+__device__ __forceinline__ uint64_t umma_desc_kmajor_noswizzle(uint32_t smem_addr)
+{
+    const uint64_t start = (smem_addr & 0x3FFFF) >> 4;
+    const uint64_t lbo = 128 >> 4, sbo = 1024 >> 4;
+    return start | (lbo << 16) | (sbo << 32) | (1ull << 46);   // bits 46-47: descriptor version 1 (sm_100); layout_type 0
+}
+// kind::tf32, fp32 accumulate, both operands K-major, M x N
+__device__ __forceinline__ uint32_t umma_idesc_tf32(int M, int N)
+{
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// stage one operand tile: rows [row0, row0+128) x K [k0, k0+32) of a row-major fp32 matrix with `pitch` floats per row,
+// as hi (the values themselves) and lo (what tf32 truncation drops) in the core-matrix layout; rows >= nrows and
+// columns >= kmax are zero
+__device__ __forceinline__ void stage_tile(const float *__restrict__ src, long long row0, long long nrows, int pitch, int k0, int kmax,
+                                           unsigned char *hi, unsigned char *lo)
+{
+    // 128 rows x 8 chunks of 16 B = 1024 chunks; thread t takes chunks t, t+128, ...: chunk id = r * 8 + c
+    for (int id = threadIdx.x; id < TC_M * (TC_KB / 4); id += TC_THREADS) {
+        const int r = id >> 3, c = id & 7;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int k = k0 + 4 * c;
+        if (row0 + r < nrows && k < kmax) v = __ldg(reinterpret_cast<const float4 *>(src + (size_t)(row0 + r) * pitch + k));
+        float4 t, l;
+        t.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+        t.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+        t.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+        t.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+        l.x = v.x - t.x; l.y = v.y - t.y; l.z = v.z - t.z; l.w = v.w - t.w;
+        const int off = (r >> 3) * 1024 + c * 128 + (r & 7) * 16;
+        *reinterpret_cast<float4 *>(hi + off) = t;      // already a tf32 value: nothing left for the tensor core to drop or round
+        *reinterpret_cast<float4 *>(lo + off) = l;
+    }
+}
+
+// out[i] = init + sum_k coef[k] * exp(-gamma * max(0, qn[i] + svn[k] - 2 q_i . sv_k))   (approximate: see above)
+// dots (optional, testing): raw q.s for the first tile of CTA 0, 128 x 128 row-major
+__global__ void __launch_bounds__(TC_THREADS, 1)
+decision_tc_kernel(const float *__restrict__ Xq, const double *__restrict__ qn, long long m, const float *__restrict__ SV,
+                   const double *__restrict__ svn, const double *__restrict__ coef, int nsv, int pitch, int d, double gamma,
+                   double init, double *__restrict__ out, float *__restrict__ dots)
+{
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char *a_hi = smem_raw, *a_lo = a_hi + TC_TILE_BYTES, *b_hi = a_lo + TC_TILE_BYTES, *b_lo = b_hi + TC_TILE_BYTES;
+    uint64_t *bar = reinterpret_cast<uint64_t *>(b_lo + TC_TILE_BYTES);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar + 1);
+    const int warp = threadIdx.x >> 5;
+    const long long row0 = (long long)blockIdx.x * TC_M;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TC_N) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t idesc = umma_idesc_tf32(TC_M, TC_N);
+    unsigned phase = 0;
+
+    const long long my_row = row0 + threadIdx.x;                     // thread t owns TMEM lane t = query row t of the tile
+    const double my_qn = my_row < m ? qn[my_row] : 0.0;
+    double sum = init;
+    const int kblocks = (d + TC_KB - 1) / TC_KB;
+
+    for (int n0 = 0; n0 < nsv; n0 += TC_N) {
+        for (int kb = 0; kb < kblocks; ++kb) {
+            stage_tile(Xq, row0, m, pitch, kb * TC_KB, d, a_hi, a_lo);
+            stage_tile(SV, n0, nsv, pitch, kb * TC_KB, d, b_hi, b_lo);
+            fence_proxy_async();                                     // generic-proxy stores -> visible to the tensor core
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < TC_KB / 8; ++ks) {             // one tf32 MMA covers K = 8 = two 16-byte core-matrix columns
+                    const uint32_t koff = ks * 2 * 128;
+                    const uint64_t ah = umma_desc_kmajor_noswizzle(smem_u32(a_hi) + koff), al = umma_desc_kmajor_noswizzle(smem_u32(a_lo) + koff);
+                    const uint64_t bh = umma_desc_kmajor_noswizzle(smem_u32(b_hi) + koff), bl = umma_desc_kmajor_noswizzle(smem_u32(b_lo) + koff);
+                    umma_tf32(tmem_base, ah, bh, idesc, (kb | ks) ? 1u : 0u);
+                    umma_tf32(tmem_base, ah, bl, idesc, 1u);
+                    umma_tf32(tmem_base, al, bh, idesc, 1u);
+                }
+                umma_commit(bar);                                    // arrives when the MMAs above have read shared memory and written TMEM
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            tc_fence_after();
+        }
+        // epilogue: thread t reads its row of the 128 x 128 accumulator, 32 columns at a time
+#pragma unroll 1
+        for (int c0 = 0; c0 < TC_N; c0 += 32) {
+            uint32_t v[32];
+            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
+                "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                  "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+                  "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+                  "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr)
+                : "memory");
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int k = n0 + c0 + j;
+                const float dot = __uint_as_float(v[j]);
+                if (dots && blockIdx.x == 0 && n0 == 0) dots[(size_t)threadIdx.x * TC_N + c0 + j] = dot;
+                if (k < nsv && my_row < m) sum = sum + coef[k] * svm_exp(-gamma * sqdist_from_dot(my_qn, svn[k], (double)dot));
+            }
+        }
+        tc_fence_before();
+        __syncthreads();                                             // every warp has drained the accumulator before the next tile overwrites it
+        tc_fence_after();
+    }
+    if (my_row < m) out[my_row] = sum;
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_N) : "memory");
+}
+
+inline size_t decision_tc_smem_bytes() { return (size_t)4 * TC_TILE_BYTES + 64 + 1024; }
+
+// |score| below the threshold: the row goes to the exact kernel
+__global__ void flag_uncertain_kernel(const double *__restrict__ scores, long long m, double threshold, int *__restrict__ list, int *__restrict__ count)
+{
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += (long long)gridDim.x * blockDim.x)
+        if (!(fabs(scores[i]) >= threshold)) list[atomicAdd(count, 1)] = (int)i;
+}
+__global__ void scatter_scores_kernel(const double *__restrict__ exact, const int *__restrict__ list, int count, double *__restrict__ scores)
+{
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < count; k += gridDim.x * blockDim.x) scores[list[k]] = exact[k];
+}
+
+} // namespace svm

@@ -420,3 +420,39 @@ def test_size_limits_and_degenerate_inputs(pkg):
         assert c == 2 and sc[0] > 0 > sc[1]
     finally:
         s.close()
+
+
+# ---- the decision function on the tensor cores (tcgen05, TF32x3) --------------------------------------------------
+
+def test_tensor_core_dot_tile(solver, dataset):
+    X, _, y = dataset(300)
+    solver.set_train_u8(X, y)
+    xs = solver.get_x_scaled()[:128].astype(np.float64)
+    ref = xs @ xs.T
+    got = solver.tc_dots().astype(np.float64)
+    err = np.abs(got - ref)
+    # three tf32 products per element, ~2 400 fp32 accumulations per dot product (the tensor core truncates them); |dot| <= ~150
+    assert err.max() <= 4e-3 and np.median(err) <= 5e-4, (err.max(), np.median(err))
+    assert np.abs(got - got.T).max() <= 4e-3
+
+
+def test_tensor_core_predict_equals_exact_labels(solver, O, dataset):
+    n, m = 3000, 1500
+    X, _, y = dataset(n)
+    Xt, _, yt = dataset(m, split=1)
+    solver.set_train_u8(X, y)
+    solver.smo_train(cache_rows=-1)
+    c_exact, s_exact = solver.predict_u8(Xt, yt)
+    try:
+        solver.set_tensor_cores(True, 0.05)
+        c_tc, s_tc = solver.predict_u8(Xt, yt)
+        rechecked = solver.tc_rechecked()
+    finally:
+        solver.set_tensor_cores(False)
+    assert c_tc == c_exact
+    assert np.array_equal(s_tc > 0, s_exact > 0)
+    assert np.max(np.abs(s_tc - s_exact)) < 2e-2                  # the tensor-core scores themselves: 2.5x under the threshold
+    unc = np.abs(s_tc) < 0.05
+    assert np.array_equal(s_tc[unc], s_exact[unc])                # rows under the threshold were re-evaluated exactly
+    assert 0 <= rechecked <= m // 4
+    print(f"tensor-core predict: max |score error| {np.max(np.abs(s_tc - s_exact)):.2e}, {rechecked} of {m} rows re-evaluated")
