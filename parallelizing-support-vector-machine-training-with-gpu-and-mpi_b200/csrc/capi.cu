@@ -438,6 +438,21 @@ static cudaError_t launch_decision_any(KernelKey k, const void *Xq, long long m,
     });
 }
 
+// few query rows: one CTA per row (falls back to the streaming kernel when the kernel values do not fit in shared memory)
+static cudaError_t launch_decision_rows_any(KernelKey k, const void *Xq, int rows, const void *SV, const double *svn, const double *coef,
+                                            int nsv, int pitch4, double gamma, double init, double *out, int max_smem, cudaStream_t stream)
+{
+    const size_t smem = (size_t)nsv * sizeof(double) + 16;
+    if (smem > (size_t)max_smem) return launch_decision_any(k, Xq, rows, SV, svn, coef, nsv, pitch4, gamma, init, nullptr, out, stream);
+    k.threads = k.f64 ? 384 : 512;
+    return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(decision_rows_kernel<XT, Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        decision_rows_kernel<XT, Q, CH><<<rows, DROWS_THREADS, smem, stream>>>(Xq, SV, svn, coef, nsv, pitch4, gamma, init, out);
+        return cudaGetLastError();
+    });
+}
+
 static cudaError_t launch_krow_any(KernelKey k, const void *X, const double *sqn, long long n, int pitch4, long long pivot, double gamma,
                                    double *out, cudaStream_t s)
 {
@@ -956,7 +971,8 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
                 e = cudaGetLastError();
             }
             if (e == cudaSuccess)
-                e = launch_decision_any(key, Xu, n_unc, ctx->svX, ctx->svn, ctx->svcoef, nsv, pitch4, ctx->params.gamma, -ctx->b, nullptr, exact, ctx->stream);
+                e = launch_decision_rows_any(key, Xu, n_unc, ctx->svX, ctx->svn, ctx->svcoef, nsv, pitch4, ctx->params.gamma, -ctx->b, exact,
+                                             ctx->max_smem_optin, ctx->stream);
             if (e == cudaSuccess) {
                 scatter_scores_kernel<<<(n_unc + 255) / 256, 256, 0, ctx->stream>>>(exact, list, n_unc, dscores);
                 e = cudaGetLastError();

@@ -21,8 +21,9 @@ namespace svm {
 constexpr int TC_M = 128;          // query rows per CTA = TMEM lanes
 constexpr int TC_N = 128;          // support vectors per tile = TMEM columns (fp32)
 constexpr int TC_KB = 32;          // K elements staged per step (8 core-matrix columns of 4 tf32 each)
-constexpr int TC_THREADS = 128;    // 4 warps: warp w reads TMEM lanes 32w .. 32w+31
+constexpr int TC_THREADS = 256;    // 8 warps stage operands; warps 0-3 also drain TMEM (warp w reads lanes 32w .. 32w+31)
 constexpr int TC_TILE_BYTES = TC_M * TC_KB * 4;   // 16 KB per operand tile
+constexpr int TC_STAGE_BYTES = 4 * TC_TILE_BYTES; // a_hi, a_lo, b_hi, b_lo
 
 // K-major, no swizzle: core matrix = 8 rows x 16 bytes (128 B, rows 16 B apart); core matrices adjacent in K are
 // 128 B apart (LBO), core matrices adjacent in M/N are 8 x 128 B = 1024 B apart (SBO)
@@ -51,41 +52,54 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar)
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+__device__ __forceinline__ void split_store(const float4 v, unsigned char *hi, unsigned char *lo, int off)
+{
+    float4 t, l;
+    t.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+    t.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+    t.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+    t.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+    l.x = v.x - t.x; l.y = v.y - t.y; l.z = v.z - t.z; l.w = v.w - t.w;
+    *reinterpret_cast<float4 *>(hi + off) = t;      // already a tf32 value: nothing left for the tensor core to drop or round
+    *reinterpret_cast<float4 *>(lo + off) = l;
+}
+
 // stage one operand tile: rows [row0, row0+128) x K [k0, k0+32) of a row-major fp32 matrix with `pitch` floats per row,
-// as hi (the values themselves) and lo (what tf32 truncation drops) in the core-matrix layout; rows >= nrows and
-// columns >= kmax are zero
+// as hi (tf32-exact part) and lo (the rest) in the core-matrix layout; rows >= nrows and columns >= kmax are zero.
+// A lane takes one row and one 32-byte sector of it (two 16-byte core-matrix rows), a warp 32 consecutive rows: the
+// eight lanes of every quarter-warp hit eight different rows of a core matrix, so the 16-byte stores are conflict-free.
 __device__ __forceinline__ void stage_tile(const float *__restrict__ src, long long row0, long long nrows, int pitch, int k0, int kmax,
                                            unsigned char *hi, unsigned char *lo)
 {
-    // 128 rows x 8 chunks of 16 B = 1024 chunks; thread t takes chunks t, t+128, ...: chunk id = r * 8 + c
-    for (int id = threadIdx.x; id < TC_M * (TC_KB / 4); id += TC_THREADS) {
-        const int r = id >> 3, c = id & 7;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < (TC_M * TC_KB / 8) / TC_THREADS; ++i) {       // 512 sectors per tile
+        const int id = threadIdx.x + TC_THREADS * i;
+        const int lane = id & 31, combo = id >> 5;
+        const int r = (combo >> 2) * 32 + lane, c = (combo & 3) * 2;
         const int k = k0 + 4 * c;
-        if (row0 + r < nrows && k < kmax) v = __ldg(reinterpret_cast<const float4 *>(src + (size_t)(row0 + r) * pitch + k));
-        float4 t, l;
-        t.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
-        t.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
-        t.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
-        t.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
-        l.x = v.x - t.x; l.y = v.y - t.y; l.z = v.z - t.z; l.w = v.w - t.w;
+        float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+        if (row0 + r < nrows) {
+            const float4 *p = reinterpret_cast<const float4 *>(src + (size_t)(row0 + r) * pitch + k);
+            if (k < kmax) v0 = __ldg(p);
+            if (k + 4 < kmax) v1 = __ldg(p + 1);
+        }
         const int off = (r >> 3) * 1024 + c * 128 + (r & 7) * 16;
-        *reinterpret_cast<float4 *>(hi + off) = t;      // already a tf32 value: nothing left for the tensor core to drop or round
-        *reinterpret_cast<float4 *>(lo + off) = l;
+        split_store(v0, hi, lo, off);
+        split_store(v1, hi, lo, off + 128);
     }
 }
 
 // out[i] = init + sum_k coef[k] * exp(-gamma * max(0, qn[i] + svn[k] - 2 q_i . sv_k))   (approximate: see above)
 // dots (optional, testing): raw q.s for the first tile of CTA 0, 128 x 128 row-major
+// Two operand buffers: while the tensor core works through the MMAs of one K step, all warps stage the next one.
 __global__ void __launch_bounds__(TC_THREADS, 1)
 decision_tc_kernel(const float *__restrict__ Xq, const double *__restrict__ qn, long long m, const float *__restrict__ SV,
                    const double *__restrict__ svn, const double *__restrict__ coef, int nsv, int pitch, int d, double gamma,
                    double init, double *__restrict__ out, float *__restrict__ dots)
 {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char *a_hi = smem_raw, *a_lo = a_hi + TC_TILE_BYTES, *b_hi = a_lo + TC_TILE_BYTES, *b_lo = b_hi + TC_TILE_BYTES;
-    uint64_t *bar = reinterpret_cast<uint64_t *>(b_lo + TC_TILE_BYTES);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar + 1);
+    uint64_t *done = reinterpret_cast<uint64_t *>(smem_raw + 2 * TC_STAGE_BYTES);   // done[b]: the MMAs that read buffer b have finished
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(done + 2);
     const int warp = threadIdx.x >> 5;
     const long long row0 = (long long)blockIdx.x * TC_M;
 
@@ -94,7 +108,8 @@ decision_tc_kernel(const float *__restrict__ Xq, const double *__restrict__ qn, 
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
+        mbar_init(&done[0], 1);
+        mbar_init(&done[1], 1);
         mbar_fence_init();
     }
     tc_fence_before();
@@ -102,69 +117,74 @@ decision_tc_kernel(const float *__restrict__ Xq, const double *__restrict__ qn, 
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t idesc = umma_idesc_tf32(TC_M, TC_N);
-    unsigned phase = 0;
 
-    const long long my_row = row0 + threadIdx.x;                     // thread t owns TMEM lane t = query row t of the tile
-    const double my_qn = my_row < m ? qn[my_row] : 0.0;
+    const long long my_row = row0 + threadIdx.x;                     // thread t < 128 owns TMEM lane t = query row t of the tile
+    const double my_qn = (threadIdx.x < TC_M && my_row < m) ? qn[my_row] : 0.0;
     double sum = init;
     const int kblocks = (d + TC_KB - 1) / TC_KB;
+    unsigned it = 0;                                                 // K steps issued so far; step `it` uses buffer it & 1
 
     for (int n0 = 0; n0 < nsv; n0 += TC_N) {
-        for (int kb = 0; kb < kblocks; ++kb) {
-            stage_tile(Xq, row0, m, pitch, kb * TC_KB, d, a_hi, a_lo);
-            stage_tile(SV, n0, nsv, pitch, kb * TC_KB, d, b_hi, b_lo);
+        for (int kb = 0; kb < kblocks; ++kb, ++it) {
+            unsigned char *buf = smem_raw + (it & 1) * TC_STAGE_BYTES;
+            if (it >= 2) mbar_wait(&done[it & 1], ((it >> 1) - 1) & 1);   // the step that last used this buffer has been consumed
+            stage_tile(Xq, row0, m, pitch, kb * TC_KB, d, buf, buf + TC_TILE_BYTES);
+            stage_tile(SV, n0, nsv, pitch, kb * TC_KB, d, buf + 2 * TC_TILE_BYTES, buf + 3 * TC_TILE_BYTES);
             fence_proxy_async();                                     // generic-proxy stores -> visible to the tensor core
             __syncthreads();
             if (threadIdx.x == 0) {
                 tc_fence_after();
+                const uint32_t a_hi = smem_u32(buf), a_lo = a_hi + TC_TILE_BYTES, b_hi = a_lo + TC_TILE_BYTES, b_lo = b_hi + TC_TILE_BYTES;
 #pragma unroll
                 for (int ks = 0; ks < TC_KB / 8; ++ks) {             // one tf32 MMA covers K = 8 = two 16-byte core-matrix columns
                     const uint32_t koff = ks * 2 * 128;
-                    const uint64_t ah = umma_desc_kmajor_noswizzle(smem_u32(a_hi) + koff), al = umma_desc_kmajor_noswizzle(smem_u32(a_lo) + koff);
-                    const uint64_t bh = umma_desc_kmajor_noswizzle(smem_u32(b_hi) + koff), bl = umma_desc_kmajor_noswizzle(smem_u32(b_lo) + koff);
+                    const uint64_t ah = umma_desc_kmajor_noswizzle(a_hi + koff), al = umma_desc_kmajor_noswizzle(a_lo + koff);
+                    const uint64_t bh = umma_desc_kmajor_noswizzle(b_hi + koff), bl = umma_desc_kmajor_noswizzle(b_lo + koff);
                     umma_tf32(tmem_base, ah, bh, idesc, (kb | ks) ? 1u : 0u);
                     umma_tf32(tmem_base, ah, bl, idesc, 1u);
                     umma_tf32(tmem_base, al, bh, idesc, 1u);
                 }
-                umma_commit(bar);                                    // arrives when the MMAs above have read shared memory and written TMEM
+                umma_commit(&done[it & 1]);                          // arrives when the MMAs above have read shared memory and written TMEM
             }
-            mbar_wait(bar, phase);
-            phase ^= 1u;
-            tc_fence_after();
         }
+        // the tile's last K step (and, the MMAs being in order, every earlier one) has landed in TMEM
+        mbar_wait(&done[(it - 1) & 1], ((it - 1) >> 1) & 1);
+        tc_fence_after();
         // epilogue: thread t reads its row of the 128 x 128 accumulator, 32 columns at a time
+        if (threadIdx.x < TC_M) {
 #pragma unroll 1
-        for (int c0 = 0; c0 < TC_N; c0 += 32) {
-            uint32_t v[32];
-            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
-                "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
-                  "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
-                  "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
-                  "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                : "r"(taddr)
-                : "memory");
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            for (int c0 = 0; c0 < TC_N; c0 += 32) {
+                uint32_t v[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
+                    "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                      "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+                      "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+                      "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr)
+                    : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int k = n0 + c0 + j;
-                const float dot = __uint_as_float(v[j]);
-                if (dots && blockIdx.x == 0 && n0 == 0) dots[(size_t)threadIdx.x * TC_N + c0 + j] = dot;
-                if (k < nsv && my_row < m) sum = sum + coef[k] * svm_exp(-gamma * sqdist_from_dot(my_qn, svn[k], (double)dot));
+                for (int j = 0; j < 32; ++j) {
+                    const int k = n0 + c0 + j;
+                    const float dot = __uint_as_float(v[j]);
+                    if (dots && blockIdx.x == 0 && n0 == 0) dots[(size_t)threadIdx.x * TC_N + c0 + j] = dot;
+                    if (k < nsv && my_row < m) sum = sum + coef[k] * svm_exp(-gamma * sqdist_from_dot(my_qn, svn[k], (double)dot));
+                }
             }
         }
         tc_fence_before();
-        __syncthreads();                                             // every warp has drained the accumulator before the next tile overwrites it
+        __syncthreads();                                             // the accumulator is drained before the next tile overwrites it
         tc_fence_after();
     }
-    if (my_row < m) out[my_row] = sum;
+    if (threadIdx.x < TC_M && my_row < m) out[my_row] = sum;
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_N) : "memory");
 }
 
-inline size_t decision_tc_smem_bytes() { return (size_t)4 * TC_TILE_BYTES + 64 + 1024; }
+inline size_t decision_tc_smem_bytes() { return (size_t)2 * TC_STAGE_BYTES + 64 + 1024; }
 
 // |score| below the threshold: the row goes to the exact kernel
 __global__ void flag_uncertain_kernel(const double *__restrict__ scores, long long m, double threshold, int *__restrict__ list, int *__restrict__ count)
