@@ -5,7 +5,8 @@
 //   svm_train --train-csv F [--test-csv F]
 //   options: --digit D (positive class, default 1: main3.cpp:49-52)  --C v  --gamma v  --eps v  --tau v
 //            --max-iter k  --sv-tol v  --cache-rows r (-1 auto, 0 off)  --limit n (first n rows: gpu_svm_main4.cu:34-38)
-//            --device i
+//            --device i  --exact (FP64 rows: the reference's own pair sequence)  --tensor-cores (predict on tcgen05)
+//            --save-model F
 #include <chrono>
 #include <cstring>
 #include <iomanip>
@@ -19,13 +20,15 @@ using namespace std::chrono;
 static void usage()
 {
     std::cerr << "usage: svm_train (--train-images F --train-labels F [--test-images F --test-labels F] | --train-csv F [--test-csv F])\n"
-                 "       [--digit D] [--C v] [--gamma v] [--eps v] [--tau v] [--max-iter k] [--sv-tol v] [--cache-rows r] [--limit n] [--device i]\n";
+                 "       [--digit D] [--C v] [--gamma v] [--eps v] [--tau v] [--max-iter k] [--sv-tol v] [--cache-rows r] [--limit n] [--device i] [--exact] [--tensor-cores] [--save-model F]\n";
 }
 
 int main(int argc, char **argv)
 {
     std::string tri, trl, tei, tel, trc, tec;
     int digit = 1;
+    bool exact = false, tensor_cores = false;
+    std::string model_path;
     long long limit = -1;
     Options &opt = options();
     for (int i = 1; i < argc; ++i) {
@@ -50,6 +53,9 @@ int main(int argc, char **argv)
         else if (a == "--cache-rows") opt.params.cache_rows = std::atoi(need("--cache-rows"));
         else if (a == "--limit") limit = std::atoll(need("--limit"));
         else if (a == "--device") opt.device = std::atoi(need("--device"));
+        else if (a == "--exact") exact = true;
+        else if (a == "--tensor-cores") tensor_cores = true;
+        else if (a == "--save-model") model_path = need("--save-model");
         else if (a == "--help" || a == "-h") { usage(); return 0; }
         else { std::cerr << "unknown option " << a << "\n"; usage(); return 1; }
     }
@@ -57,6 +63,8 @@ int main(int argc, char **argv)
     if (use_idx == !trc.empty() || (use_idx && trl.empty())) { usage(); return 1; }
 
     svmb200_ctx *ctx = context();
+    svmb200_set_exact(ctx, exact ? 1 : 0);
+    if (tensor_cores) svmb200_set_tensor_cores(ctx, 1, 0.05);
     size_t n_features = 0, n = 0;
     std::vector<uint8_t> x8, digits;
     std::vector<double> x_train;
@@ -95,6 +103,7 @@ int main(int argc, char **argv)
     std::cout << "(b_high - b_low)/2*1e10 = " << std::fixed << std::setprecision(15) << (st.b_high - st.b_low) / 2 * 1e10 << std::endl;
     std::cout << "Final SV count = " << st.n_sv << "\n";                                                 // main3.cpp:370
     auto end1 = high_resolution_clock::now();
+    if (!model_path.empty() && svmb200_save_model(ctx, model_path.c_str()) != SVMB200_OK) { std::cerr << svmb200_last_error(ctx) << std::endl; return 2; }
 
     if (!tei.empty() || !tec.empty()) {
         std::vector<uint8_t> t8, tdig;
