@@ -34,3 +34,14 @@ def test_row_sharded_smo_is_bit_identical_to_one_gpu(world, tmp_path):
             assert v["alpha_equal"] and v["b_equal"] and v["trace_equal"] and v["sv_equal"], (label, v)
         assert res["cache_on"]["cache_hits"] > 0 and res["cache_off"]["cache_hits"] == 0
     assert len({r["correct"] for r in allres}) == 1
+
+
+@pytest.mark.parametrize("world,n", [(2, 11), (3, 100)])
+def test_row_sharding_host_logic_over_gloo(world, n, tmp_path):
+    """CPU: the plumbing around the sharded solver (IPC-handle all_gather, row ranges, alpha all_gather, model install)."""
+    out = tmp_path / "logic.json"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29300 + world), os.path.join(ROOT, "tests", "shard_logic_worker.py"), str(n), str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, OMP_NUM_THREADS="1"))
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert json.load(open(out)) == [True] * world
