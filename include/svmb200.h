@@ -67,6 +67,9 @@ typedef struct {
     int32_t trace_cap;    /* record the first trace_cap (i_high, i_low) pairs for svmb200_get_trace */
     int32_t l2_persist;   /* 0 = stream X with evict-first; 1 = keep a leading fraction of every
                              block's rows resident in L2 (evict-last); -1 = auto */
+    int32_t keep_cache;   /* 1 = start from the kernel rows the previous svmb200_smo_train on this X left in the
+                             row cache (kernel values do not depend on the labels or on C): one-vs-rest over
+                             several digits, C sweeps.  Needs the same cache_rows, accum_chunk and gamma. */
 } svmb200_params;
 
 typedef struct {
@@ -102,6 +105,10 @@ int svmb200_set_train_u8 (svmb200_ctx *ctx, const uint8_t *X, const int32_t *y, 
                           double *min_out, double *max_out);
 int svmb200_set_train_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y, int64_t n, int32_t d,
                           double *min_out, double *max_out);
+/* New +-1 labels for the rows already uploaded (the reference handles one digit, main3.cpp:49-52; one-vs-rest over all
+ * ten digits is ten label vectors on the same X).  The kernel-row cache survives (see svmb200_params.keep_cache). */
+int svmb200_set_labels(svmb200_ctx *ctx, const int32_t *y);
+
 /* Storage precision of X for the NEXT svmb200_set_train_* call: 0 (default) = fp32 rows, the fast path the
  * roofline numbers are quoted on; 1 = FP64 rows ("exact"): twice the bytes per iteration, K formed from FP64 squared
  * differences as in main3.cpp:97-100, so that the selected (i_high, i_low) sequence is the reference's own

@@ -23,7 +23,7 @@ class Params(C.Structure):
     _fields_ = [("C", C.c_double), ("gamma", C.c_double), ("eps", C.c_double), ("tau", C.c_double),
                 ("max_iter", C.c_int32), ("sv_tol", C.c_double), ("wss", C.c_int32), ("warm_start", C.c_int32),
                 ("cache_rows", C.c_int32), ("accum_chunk", C.c_int32), ("trace_cap", C.c_int32),
-                ("l2_persist", C.c_int32)]
+                ("l2_persist", C.c_int32), ("keep_cache", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -74,6 +74,7 @@ def load_library():
     L.svmb200_set_train_f64.argtypes = [vp, vp, vp, i64, i32, vp, vp]
     L.svmb200_set_train_scaled_f64.argtypes = [vp, vp, vp, i64, i32]
     L.svmb200_set_exact.argtypes = [vp, i32]
+    L.svmb200_set_labels.argtypes = [vp, vp]
     L.svmb200_minmax_f64.argtypes = [vp, vp, i64, i32, vp, vp]
     L.svmb200_scale_f64.argtypes = [vp, vp, vp, vp, i64, i32]
     L.svmb200_smo_train.argtypes = [vp, C.POINTER(Params), vp, C.POINTER(dbl), C.POINTER(Stats)]
@@ -138,6 +139,11 @@ class Solver:
             raise SvmB200Error(f"{what} = {rc}: {self.L.svmb200_last_error(self.h).decode()}")
 
     # ---- ingest
+    def set_labels(self, y):
+        y = np.ascontiguousarray(y, dtype=np.int32)
+        assert y.size == self.n
+        self._ck(self.L.svmb200_set_labels(self.h, _ptr(y)), "set_labels")
+
     def set_exact(self, enable: bool):
         """FP64 storage of X for the next set_train_* (the exact path); False = fp32 (default)."""
         self._ck(self.L.svmb200_set_exact(self.h, 1 if enable else 0), "set_exact")

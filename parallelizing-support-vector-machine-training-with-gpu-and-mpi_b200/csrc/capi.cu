@@ -56,6 +56,11 @@ struct svmb200_ctx {
     long long *cacheq = nullptr;
     double *cacheK = nullptr;
     size_t cacheK_elems = 0;
+    // a cache kept across runs on the same X (kernel values do not depend on labels or on C): valid for (cap, chunk, gamma)
+    bool cache_valid = false;
+    int cache_valid_cap = 0, cache_valid_chunk = 0;
+    double cache_valid_gamma = 0.0;
+    long long cache_counter = 0;
     Rec *rec = nullptr;
     int rec_blocks = 0;
     SmoResult *result = nullptr;
@@ -148,6 +153,7 @@ void svmb200_default_params(svmb200_params *p)
     p->accum_chunk = 0;
     p->trace_cap = 0;
     p->l2_persist = 0;
+    p->keep_cache = 0;
 }
 
 const char *svmb200_last_error(const svmb200_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
@@ -245,6 +251,7 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
     ctx->have_stats = false;
     ctx->sqn_chunk = 0;
     ctx->model_ready = false;
+    ctx->cache_valid = false;
     return 0;
 }
 
@@ -316,6 +323,19 @@ int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32
 }
 
 } // extern "C"
+
+// new labels for the rows already uploaded (one-vs-rest over several digits on one X): the kernel-row cache stays valid
+extern "C" int svmb200_set_labels(svmb200_ctx *ctx, const int32_t *y)
+{
+    if (!ctx || !y) return SVMB200_EINVAL;
+    if (!ctx->have_train) FAIL(SVMB200_ESTATE, "svmb200_set_labels called before svmb200_set_train_*");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(ctx->y, y, (size_t)ctx->n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->trained = false;
+    ctx->model_ready = false;
+    return SVMB200_OK;
+}
 
 // storage precision of X for the NEXT svmb200_set_train_*: 0 = fp32 (default), 1 = FP64 ("exact")
 extern "C" int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable)
@@ -583,6 +603,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         ctx->trace_alloc = trace_cap;
     }
 
+    // keep_cache: reuse the kernel rows cached by the previous run on this X (same capacity, arithmetic and gamma)
+    const bool keep = params->keep_cache && cache_cap > 0 && ctx->cache_valid && ctx->cache_valid_cap == cache_cap &&
+                      ctx->cache_valid_chunk == CH && ctx->cache_valid_gamma == params->gamma && ctx->shard_world == 1;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     if (int rc = ensure_norms(ctx, CH)) return rc;
     CK(cudaMemsetAsync(ctx->rec, 0, (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 256, ctx->stream));
@@ -597,14 +620,14 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
             if (alpha[j] != 0.0) { nz.push_back((int)j); nzy.push_back(y_host[j]); }
         if (int rc = build_sv_block(ctx, nz, alpha, nzy)) return rc;
         ctx->model_ready = false;
-        init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 0, 0);
+        init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, keep ? nullptr : ctx->cacheq, 0, 0);
         ctx->launches += 1;
         CK(cudaGetLastError());
         CK(launch_decision_any(KernelKey{ctx->x_f64, Q, CH, 0}, ctx->X, n, ctx->svX, ctx->svn, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
                                ctx->y, ctx->f, ctx->stream));
         ctx->launches += 1;
     } else {
-        init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, ctx->cacheq, 1, 1);
+        init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, keep ? nullptr : ctx->cacheq, 1, 1);
         ctx->launches += 1;
         CK(cudaGetLastError());
     }
@@ -616,6 +639,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     a.arrive = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
     a.n = n; a.pitch4 = ctx->pitch4; a.kslots = kslots; a.cache_cap = cache_cap; a.trace_cap = trace_cap;
     a.max_iter = params->max_iter;
+    a.cache_counter0 = keep ? ctx->cache_counter : 0;
     a.C = params->C; a.gamma = params->gamma; a.eps = params->eps; a.tau = params->tau;
     a.policy_stream = L2_EVICT_FIRST; a.policy_keep = L2_EVICT_LAST; a.keep_per_1024 = 0;
     {
@@ -667,6 +691,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     ctx->sv_ids.clear();
     for (long long i = 0; i < n; ++i)            // get_SV_indices, main3.cpp:297-304
         if (alpha[i] > params->sv_tol) ctx->sv_ids.push_back((int)i);
+    ctx->cache_valid = cache_cap > 0 && ctx->shard_world == 1;
+    ctx->cache_valid_cap = cache_cap; ctx->cache_valid_chunk = CH; ctx->cache_valid_gamma = params->gamma;
+    ctx->cache_counter = r.cache_counter;
     ctx->trace_count = std::min(trace_cap, r.num_iter - 1);
     ctx->trained = true;
     ctx->model_ready = false;

@@ -58,6 +58,7 @@ struct SmoArgs {
     int pitch4;            // 16-byte groups per row
     int kslots;            // ring depth per warp (2..SMO_KSLOTS_MAX), chosen so the ring fits in shared memory
     int cache_cap;
+    long long cache_counter0;  // allocation number to start from (> 0 when the cache is kept from an earlier run on the same X)
     int trace_cap;
     int max_iter;
     double C, gamma, eps, tau;
@@ -439,7 +440,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     int stop = 0;
     double b_high = 0.0, b_low = 0.0;    // uninitialised in the reference (main3.cpp:188-189)
     long long i_high = a.n, i_low = a.n;
-    long long cache_counter = 0;         // replicated: every CTA sees the same hit/miss sequence
+    long long cache_counter = a.cache_counter0;   // replicated: every CTA sees the same hit/miss sequence
     long long x_passes = 0, cache_hits = 0;
 
     for (;;) {

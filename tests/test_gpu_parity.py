@@ -164,6 +164,28 @@ def test_same_cache_capacity_on_a_bigger_problem(solver, dataset):
         assert np.array_equal(on["alpha"], off["alpha"]) and on["b"] == off["b"]
 
 
+def test_one_vs_rest_with_a_kept_cache(solver, pkg, dataset):
+    """Ten label vectors on one X: the kernel-row cache is label-independent, so keeping it changes no result."""
+    X, dg, _ = dataset(1500)
+    solver.set_train_u8(X, pkg.datagen.binary_labels(dg, 0))
+    fresh, kept, passes = [], [], []
+    for digit in range(4):
+        solver.set_labels(pkg.datagen.binary_labels(dg, digit))
+        fresh.append(solver.smo_train(cache_rows=0))
+    solver.set_train_u8(X, pkg.datagen.binary_labels(dg, 0))
+    for digit in range(4):
+        solver.set_labels(pkg.datagen.binary_labels(dg, digit))
+        o = solver.smo_train(cache_rows=-1, keep_cache=1)
+        kept.append(o); passes.append(o["x_passes"])
+    for a, b in zip(fresh, kept):
+        assert np.array_equal(a["alpha"], b["alpha"]) and a["b"] == b["b"] and a["num_iter"] == b["num_iter"]
+    alone = []
+    for digit in range(4):
+        solver.set_labels(pkg.datagen.binary_labels(dg, digit))
+        alone.append(solver.smo_train(cache_rows=-1)["x_passes"])
+    assert passes[0] == alone[0] and all(p <= q for p, q in zip(passes[1:], alone[1:])) and sum(passes[1:]) < sum(alone[1:])
+
+
 def test_warm_start_matches_oracle(solver, O, dataset):
     """init=false: alpha in/out, f rebuilt from alpha (mpi_svm_main2.cpp:167-183)."""
     n = 800
