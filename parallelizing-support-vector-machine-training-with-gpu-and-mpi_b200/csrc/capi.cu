@@ -94,6 +94,13 @@ struct svmb200_ctx {
     // generic scratch
     void *scratch = nullptr;
     size_t scratch_bytes = 0;
+    // grow-only work areas of the decision function (query rows, scores, packed panels; [1] = the rows sent to the exact kernel):
+    // svmb200_predict_* allocates only when a call needs more than any earlier one did
+    void *work[2] = {nullptr, nullptr};
+    size_t work_bytes[2] = {0, 0};
+    unsigned char *svP = nullptr;        // the model's support vectors packed for the tensor-core kernel
+    size_t svP_bytes = 0;
+    bool svP_valid = false;
     int launches = 0;
 };
 
@@ -124,6 +131,18 @@ static int ensure_scratch(svmb200_ctx *ctx, size_t bytes)
     ctx->scratch_bytes = 0;
     CK(cudaMalloc(&ctx->scratch, bytes));
     ctx->scratch_bytes = bytes;
+    return 0;
+}
+
+static int ensure_work(svmb200_ctx *ctx, int which, size_t bytes)
+{
+    if (bytes <= ctx->work_bytes[which]) return 0;
+    if (ctx->work[which]) CK(cudaFree(ctx->work[which]));
+    ctx->work[which] = nullptr;
+    ctx->work_bytes[which] = 0;
+    bytes += bytes / 8;                                        // headroom: slightly larger batches do not reallocate
+    CK(cudaMalloc(&ctx->work[which], bytes));
+    ctx->work_bytes[which] = bytes;
     return 0;
 }
 
@@ -210,6 +229,7 @@ void svmb200_destroy(svmb200_ctx *ctx)
         if (p != ctx->shard_rank && ctx->peer_mailbox[p]) cudaIpcCloseMemHandle(ctx->peer_mailbox[p]);
     cudaFree(ctx->mailbox);
     cudaFree(ctx->svX); cudaFree(ctx->svcoef); cudaFree(ctx->scratch);
+    cudaFree(ctx->work[0]); cudaFree(ctx->work[1]); cudaFree(ctx->svP);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -520,6 +540,7 @@ static int resolve_chunk(int c)
 static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const double *alpha_host, const std::vector<int> &y_host_sv)
 {
     const int nsv = (int)ids.size();
+    ctx->svP_valid = false;
     if (nsv > ctx->sv_alloc) {
         if (dev_free(ctx, ctx->svX) || dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn)) return SVMB200_ECUDA;
         const int cap = std::max(nsv, 1024);
@@ -652,10 +673,6 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         if (x_bytes <= 96.0 * 1024 * 1024) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
         else if (persist) a.keep_per_1024 = (int)(1024.0 * l2_keep_budget / x_bytes);
     }
-    a.l2_ahead = 0;
-    if (const char *e = getenv("SVMB200_L2AHEAD")) a.l2_ahead = std::max(0, std::min(32, atoi(e)));
-    a.l2_burst = 0;
-    if (const char *e = getenv("SVMB200_L2BURST")) a.l2_burst = std::max(0, std::min(16, atoi(e)));
     a.peers = ctx->shard_world; a.rank = ctx->shard_rank;
     a.row_begin = n * ctx->shard_rank / ctx->shard_world;
     a.row_end = n * (ctx->shard_rank + 1) / ctx->shard_world;
@@ -847,6 +864,7 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
     ctx->n = 0; ctx->d = d; ctx->pitch4 = h.pitch4; ctx->x_f64 = h.x_f64 != 0; ctx->have_train = false; ctx->sqn_chunk = 0; ctx->sv_alloc = std::max(nsv, 1);
     CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
     CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
+    ctx->svP_valid = false;
     CK(cudaMalloc(&ctx->svX, (size_t)ctx->sv_alloc * h.pitch4 * 16));
     CK(cudaMalloc(&ctx->svcoef, (size_t)ctx->sv_alloc * sizeof(double)));
     CK(cudaMalloc(&ctx->svn, (size_t)ctx->sv_alloc * sizeof(double)));
@@ -885,6 +903,60 @@ extern "C" int svmb200_set_tensor_cores(svmb200_ctx *ctx, int32_t enable, double
     return SVMB200_OK;
 }
 
+// tensor-core scores of m query rows against the current model's support-vector block.  Default: operands packed once
+// (tc_pack_kernel) and streamed by bulk copies through the warp-specialised kernel; SVMB200_TC_KERNEL=staged selects
+// the earlier kernel that splits and stages tiles itself.
+static size_t tc_panel_bytes(const svmb200_ctx *ctx, long long rows)
+{
+    return (size_t)((rows + TC_M - 1) / TC_M) * ((ctx->d + TC_KB - 1) / TC_KB) * TCP_PANEL_BYTES;
+}
+
+// qP: tc_panel_bytes(m) of device memory for the packed query rows.  svP: packed support vectors, or NULL = the current
+// model's (ctx->svX), packed once per model and kept.
+static int launch_tc_scores(svmb200_ctx *ctx, const float *Xq, const double *qn, long long m, unsigned char *qP, const float *svX,
+                            const double *svn, const double *svcoef, int nsv, unsigned char *svP, double init, double *dscores, float *dots)
+{
+    const int pitch = ctx->pitch4 * 4;
+    const char *which = getenv("SVMB200_TC_KERNEL");
+    if (which && !strcmp(which, "staged")) {
+        CK(cudaFuncSetAttribute(decision_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_smem_bytes()));
+        decision_tc_kernel<<<(unsigned)((m + TC_M - 1) / TC_M), TC_THREADS, decision_tc_smem_bytes(), ctx->stream>>>(
+            Xq, qn, m, svX, svn, svcoef, nsv, pitch, ctx->d, ctx->params.gamma, init, dscores, dots);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+        return 0;
+    }
+    const int kblocks = (ctx->d + TC_KB - 1) / TC_KB;
+    const int blocks = ctx->num_sms * 8;
+    if (!svP) {
+        if (!ctx->svP_valid) {
+            const size_t need = tc_panel_bytes(ctx, nsv);
+            if (need > ctx->svP_bytes) {
+                if (dev_free(ctx, ctx->svP)) return SVMB200_ECUDA;
+                ctx->svP_bytes = 0;
+                CK(cudaMalloc(&ctx->svP, need + need / 8));
+                ctx->svP_bytes = need + need / 8;
+            }
+            tc_pack_kernel<<<blocks, 256, 0, ctx->stream>>>(svX, nsv, pitch, ctx->d, kblocks, ctx->svP);
+            ctx->launches += 1;
+            CK(cudaGetLastError());
+            ctx->svP_valid = true;
+        }
+        svP = ctx->svP;
+    } else {
+        tc_pack_kernel<<<blocks, 256, 0, ctx->stream>>>(svX, nsv, pitch, ctx->d, kblocks, svP);
+        ctx->launches += 1;
+    }
+    tc_pack_kernel<<<blocks, 256, 0, ctx->stream>>>(Xq, m, pitch, ctx->d, kblocks, qP);
+    CK(cudaGetLastError());
+    CK(cudaFuncSetAttribute(decision_tc_pipelined_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_pipelined_smem_bytes()));
+    decision_tc_pipelined_kernel<<<(unsigned)((m + TC_M - 1) / TC_M), TCP_THREADS, decision_tc_pipelined_smem_bytes(), ctx->stream>>>(
+        qP, qn, m, svP, svn, svcoef, nsv, kblocks, ctx->params.gamma, init, dscores, dots);
+    ctx->launches += 2;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 // introspection: the raw tensor-core dot products of the first 128 training rows against themselves (128 x 128),
 // and how many rows the last svmb200_predict_* sent to the exact kernel
 extern "C" int svmb200_debug_tc_dots(svmb200_ctx *ctx, float *dots, int64_t *rechecked)
@@ -896,16 +968,15 @@ extern "C" int svmb200_debug_tc_dots(svmb200_ctx *ctx, float *dots, int64_t *rec
     CK(cudaSetDevice(ctx->device));
     const long long rows = std::min<long long>(ctx->n, TC_M);
     if (int rc = ensure_norms(ctx, DEFAULT_CHUNK)) return rc;
-    if (int rc = ensure_scratch(ctx, (size_t)TC_M * TC_N * sizeof(float) + (size_t)TC_M * 2 * sizeof(double))) return rc;
-    float *d_dots = static_cast<float *>(ctx->scratch);
+    const size_t head = (size_t)TC_M * TC_N * sizeof(float) + (size_t)TC_M * 2 * sizeof(double), panel = tc_panel_bytes(ctx, rows);
+    if (int rc = ensure_work(ctx, 0, head + 2 * panel)) return rc;
+    float *d_dots = static_cast<float *>(ctx->work[0]);
     double *coef = reinterpret_cast<double *>(d_dots + TC_M * TC_N), *out = coef + TC_M;
-    CK(cudaMemsetAsync(ctx->scratch, 0, (size_t)TC_M * TC_N * sizeof(float) + (size_t)TC_M * 2 * sizeof(double), ctx->stream));
-    CK(cudaFuncSetAttribute(decision_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_smem_bytes()));
-    decision_tc_kernel<<<1, TC_THREADS, decision_tc_smem_bytes(), ctx->stream>>>(static_cast<const float *>(ctx->X), ctx->sqn, rows,
-                                                                               static_cast<const float *>(ctx->X), ctx->sqn, coef, (int)rows,
-                                                                               ctx->pitch4 * 4, ctx->d, 0.0, 0.0, out, d_dots);
-    ctx->launches += 1;
-    CK(cudaGetLastError());
+    unsigned char *qP = static_cast<unsigned char *>(ctx->work[0]) + head;
+    CK(cudaMemsetAsync(ctx->work[0], 0, head, ctx->stream));
+    if (int rc = launch_tc_scores(ctx, static_cast<const float *>(ctx->X), ctx->sqn, rows, qP, static_cast<const float *>(ctx->X), ctx->sqn, coef,
+                                  (int)rows, qP + panel, 0.0, out, d_dots))
+        return rc;
     CK(cudaMemcpyAsync(dots, d_dots, (size_t)TC_M * TC_N * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return SVMB200_OK;
@@ -953,83 +1024,67 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     const int pitch4 = ctx->pitch4;
     if (int rc = ensure_model(ctx)) return rc;
 
-    void *Xq = nullptr;
-    double *dscores = nullptr;
-    int *dy = nullptr, *dcorrect = nullptr;
-    CK(cudaMalloc(&Xq, (size_t)m * pitch4 * 16));
-    CK(cudaMalloc(&dscores, (size_t)m * sizeof(double)));
-    CK(cudaMalloc(&dy, (size_t)m * sizeof(int) + sizeof(int)));
-    dcorrect = dy + m;
-    int rc = ingest<T>(ctx, X, m, false, scale, Xq);
-    cudaError_t e = cudaSuccess;
+    // one grow-only work area: query rows | scores | labels + counter | (tensor cores: norms | list + counter | packed rows)
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const bool use_tc = ctx->tc_predict && !ctx->x_f64 && ctx->model_nsv > 0;
+    const size_t o_x = 0, o_scores = o_x + up((size_t)m * pitch4 * 16), o_y = o_scores + up((size_t)m * sizeof(double)),
+                 o_qn = o_y + up(((size_t)m + 1) * sizeof(int)), o_list = o_qn + (use_tc ? up((size_t)m * sizeof(double)) : 0),
+                 o_panel = o_list + (use_tc ? up(((size_t)m + 1) * sizeof(int)) : 0), o_end = o_panel + (use_tc ? tc_panel_bytes(ctx, m) : 0);
+    if (int rc = ensure_work(ctx, 0, o_end)) return rc;
+    char *w = static_cast<char *>(ctx->work[0]);
+    void *Xq = w + o_x;
+    double *dscores = reinterpret_cast<double *>(w + o_scores);
+    int *dy = reinterpret_cast<int *>(w + o_y), *dcorrect = dy + m;
+    if (int rc = ingest<T>(ctx, X, m, false, scale, Xq)) return rc;
     const KernelKey key{ctx->x_f64, q_for_pitch(pitch4, ctx->x_f64), ctx->params.accum_chunk, 0};
-    if (!rc && ctx->tc_predict && !ctx->x_f64 && ctx->model_nsv > 0) {
+    if (use_tc) {
         // tensor cores first (TF32x3, approximate), then the exact kernel for every row whose |score| is under the threshold
         const int nsv = ctx->model_nsv;
-        double *qn = nullptr, *exact = nullptr;
-        int *list = nullptr;
-        float *Xu = nullptr;
-        e = cudaMalloc(&qn, (size_t)m * sizeof(double));
-        if (e == cudaSuccess) e = cudaMalloc(&list, ((size_t)m + 1) * sizeof(int));
-        if (e == cudaSuccess) e = launch_sqnorm_any(key, static_cast<const float *>(Xq), m, pitch4, qn, ctx->stream);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(decision_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_smem_bytes());
-        if (e == cudaSuccess) {
-            decision_tc_kernel<<<(unsigned)((m + TC_M - 1) / TC_M), TC_THREADS, decision_tc_smem_bytes(), ctx->stream>>>(
-                static_cast<const float *>(Xq), qn, m, static_cast<const float *>(ctx->svX), ctx->svn, ctx->svcoef, nsv, pitch4 * 4, ctx->d,
-                ctx->params.gamma, -ctx->b, dscores, nullptr);
-            e = cudaGetLastError();
-        }
+        double *qn = reinterpret_cast<double *>(w + o_qn);
+        int *list = reinterpret_cast<int *>(w + o_list);
+        CK(launch_sqnorm_any(key, static_cast<const float *>(Xq), m, pitch4, qn, ctx->stream));
+        if (int rc = launch_tc_scores(ctx, static_cast<const float *>(Xq), qn, m, reinterpret_cast<unsigned char *>(w + o_panel),
+                                      static_cast<const float *>(ctx->svX), ctx->svn, ctx->svcoef, nsv, nullptr, -ctx->b, dscores, nullptr))
+            return rc;
         int n_unc = 0;
-        if (e == cudaSuccess) e = cudaMemsetAsync(list + m, 0, sizeof(int), ctx->stream);
-        if (e == cudaSuccess) {
-            flag_uncertain_kernel<<<std::min<long long>((m + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(dscores, m, ctx->tc_threshold, list, list + m);
-            e = cudaGetLastError();
-        }
-        if (e == cudaSuccess) e = cudaMemcpyAsync(&n_unc, list + m, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        ctx->launches += 3;
-        if (e == cudaSuccess && n_unc > 0) {
-            e = cudaMalloc(&Xu, (size_t)n_unc * pitch4 * 16);
-            if (e == cudaSuccess) e = cudaMalloc(&exact, (size_t)n_unc * sizeof(double));
-            if (e == cudaSuccess) {
-                const long long total = (long long)n_unc * pitch4;
-                gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
-                    Xq, nullptr, pitch4, list, n_unc, Xu, qn /* norms unused by the exact kernel: scratch */);
-                e = cudaGetLastError();
-            }
-            if (e == cudaSuccess)
-                e = launch_decision_rows_any(key, Xu, n_unc, ctx->svX, ctx->svn, ctx->svcoef, nsv, pitch4, ctx->params.gamma, -ctx->b, exact,
-                                             ctx->max_smem_optin, ctx->stream);
-            if (e == cudaSuccess) {
-                scatter_scores_kernel<<<(n_unc + 255) / 256, 256, 0, ctx->stream>>>(exact, list, n_unc, dscores);
-                e = cudaGetLastError();
-            }
+        CK(cudaMemsetAsync(list + m, 0, sizeof(int), ctx->stream));
+        flag_uncertain_kernel<<<std::min<long long>((m + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(dscores, m, ctx->tc_threshold, list, list + m);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&n_unc, list + m, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->launches += 2;
+        if (n_unc > 0) {
+            const size_t xu_bytes = up((size_t)n_unc * pitch4 * 16);
+            if (int rc = ensure_work(ctx, 1, xu_bytes + (size_t)n_unc * sizeof(double))) return rc;
+            void *Xu = ctx->work[1];
+            double *exact = reinterpret_cast<double *>(static_cast<char *>(ctx->work[1]) + xu_bytes);
+            const long long total = (long long)n_unc * pitch4;
+            gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+                Xq, nullptr, pitch4, list, n_unc, Xu, qn /* norms unused by the exact kernel: scratch */);
+            CK(cudaGetLastError());
+            CK(launch_decision_rows_any(key, Xu, n_unc, ctx->svX, ctx->svn, ctx->svcoef, nsv, pitch4, ctx->params.gamma, -ctx->b, exact,
+                                        ctx->max_smem_optin, ctx->stream));
+            scatter_scores_kernel<<<(n_unc + 255) / 256, 256, 0, ctx->stream>>>(exact, list, n_unc, dscores);
+            CK(cudaGetLastError());
             ctx->launches += 3;
         }
         ctx->tc_rechecked = n_unc;
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        cudaFree(qn); cudaFree(list); cudaFree(Xu); cudaFree(exact);
-    } else if (!rc) {
-        e = launch_decision_any(key, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv,
-                                pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores, ctx->stream);
+    } else {
+        CK(launch_decision_any(key, Xq, m, ctx->svX, ctx->svn, ctx->svcoef, ctx->model_nsv, pitch4, ctx->params.gamma, -ctx->b, nullptr, dscores,
+                               ctx->stream));
         ctx->launches += 1;
     }
     int host_correct = 0;
-    if (!rc && e == cudaSuccess && y_test) {
-        e = cudaMemcpyAsync(dy, y_test, (size_t)m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
-        if (e == cudaSuccess) e = cudaMemsetAsync(dcorrect, 0, sizeof(int), ctx->stream);
-        if (e == cudaSuccess) {
-            count_correct_kernel<<<std::min<long long>((m + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(dscores, dy, m, ge_zero, dcorrect);
-            ctx->launches += 1;
-            e = cudaGetLastError();
-        }
-        if (e == cudaSuccess) e = cudaMemcpyAsync(&host_correct, dcorrect, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    if (y_test) {
+        CK(cudaMemcpyAsync(dy, y_test, (size_t)m * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemsetAsync(dcorrect, 0, sizeof(int), ctx->stream));
+        count_correct_kernel<<<std::min<long long>((m + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(dscores, dy, m, ge_zero, dcorrect);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&host_correct, dcorrect, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     }
-    if (!rc && e == cudaSuccess && scores) e = cudaMemcpyAsync(scores, dscores, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
-    if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(Xq); cudaFree(dscores); cudaFree(dy);
-    if (rc) return rc;
-    if (e != cudaSuccess) FAIL(SVMB200_ECUDA, "predict failed: %s", cudaGetErrorString(e));
+    if (scores) CK(cudaMemcpyAsync(scores, dscores, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     if (correct) *correct = host_correct;
     return SVMB200_OK;
 }

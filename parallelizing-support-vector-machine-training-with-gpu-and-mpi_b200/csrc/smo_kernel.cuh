@@ -65,8 +65,6 @@ struct SmoArgs {
     unsigned long long policy_stream;  // L2 policy for the streamed part of every CTA's rows
     unsigned long long policy_keep;    // L2 policy for the leading keep_frac of every warp's rows
     int keep_per_1024;                 // rows (per 1024) of each warp's range loaded with policy_keep
-    int l2_ahead;                      // rows requested into L2 ahead of the shared-memory ring (0 = off)
-    int l2_burst;                      // rows per warp requested into L2 when the warp finishes its pass (0 = off)
     // ---- multi-GPU row sharding (peers == 1: single GPU) ----
     int peers;                          // GPUs sharing the rows
     int rank;                           // this GPU
@@ -395,7 +393,6 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     const long long w1 = r0 + (long long)(warp + 1) * R / WARPS;
     const int m = (int)(w1 - w0);
     const int keep_rows = (int)(((long long)m * a.keep_per_1024) >> 10);
-    const int ahead = (a.l2_ahead > 0 && m > a.kslots + a.l2_ahead) ? a.l2_ahead : 0;
 
     unsigned char *my_slots = slots + (size_t)warp * KS * row_bytes;
     uint64_t *my_bars = bars + warp * SMO_KSLOTS_MAX;
@@ -415,20 +412,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
             bulk_g2s(my_slots + (size_t)s * row_bytes, Xb + (size_t)(w0 + pf_row) * row_bytes, (unsigned)row_bytes,
                      &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
-            if (ahead > 0) {             // and the row `ahead` places further on goes from HBM into L2
-                int r = pf_row + ahead;
-                if (r >= m) r -= m;
-                bulk_prefetch_l2(Xb + (size_t)(w0 + r) * row_bytes, (unsigned)row_bytes, a.policy_stream);
-            }
         }
         if (++pf_row == m) pf_row = 0;
     };
-    if (m > 0) {
-        if (lane == 0)
-            for (int r = KS; r < KS + ahead; ++r)
-                bulk_prefetch_l2(Xb + (size_t)(w0 + r) * row_bytes, (unsigned)row_bytes, a.policy_stream);
+    if (m > 0)
         for (int s = 0; s < KS; ++s) issue_into(s);
-    }
 
     // ---- exchange 0: selection over the initial state (main3.cpp:203-204 in the first iteration)
     LocalBest mine;
@@ -596,15 +584,6 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
                     if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
                     best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
-                }
-            }
-            if (a.l2_burst > 0 && lane == 0 && m > KS + a.l2_burst) {
-                // the pass is over for this warp: the rows it will want right after the ring go from HBM to L2 while
-                // the CTAs are in the record exchange
-                int r = pf_row;
-                for (int k = 0; k < a.l2_burst; ++k) {
-                    bulk_prefetch_l2(Xb + (size_t)(w0 + r) * row_bytes, (unsigned)row_bytes, a.policy_stream);
-                    if (++r == m) r = 0;
                 }
             }
         } else {
