@@ -218,21 +218,30 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
     }
 }
 
-// ---- the same decision values for a FEW query rows (the tensor-core path's re-evaluation list): one CTA per query
-// row, its warps share out the support vectors (rows read straight from L2), the kernel values go to shared memory
-// and one thread adds them up in k order -- the same operations in the same order as decision_kernel, hence the
-// same bits, but ~25x less latency than one warp walking all support vectors.
+// ---- the same decision values for a FEW query rows (the tensor-core path's re-evaluation list): `parts` CTAs per
+// query row share out the support vectors (rows read straight from L2, two in flight per warp), the products
+// coef_k K(q, sv_k) go to shared memory (parts == 1) or to `kprod` in global memory, and one thread of the row's last
+// CTA to finish adds them up in k order -- the same operations in the same order as decision_kernel, hence the same
+// bits, at a small fraction of the latency of one warp walking all support vectors.
+// kprod: [rows][nsv] doubles, done: [rows] ints zeroed before the launch (both unused when parts == 1).
 constexpr int DROWS_THREADS = 512;
 template <typename XT, int Q, int CH>
 __global__ void __launch_bounds__(DROWS_THREADS, 1)
 decision_rows_kernel(const void *__restrict__ Xq, const void *__restrict__ SV, const double *__restrict__ svn,
-                     const double *__restrict__ coef, int nsv, int pitch4, double gamma, double init, double *__restrict__ out)
+                     const double *__restrict__ coef, int nsv, int pitch4, double gamma, double init, double *__restrict__ out,
+                     int parts, double *__restrict__ kprod, int *__restrict__ done)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double *kbuf = reinterpret_cast<double *>(smem_raw);
+    __shared__ int is_last;
     using Vec = typename RowVec<XT>::type;
+    constexpr int W = DROWS_THREADS / 32;
+    constexpr bool TWO = sizeof(XT) == 4 && Q <= 8;                            // registers for a second row in flight
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const Vec *xq = reinterpret_cast<const Vec *>(Xq) + (size_t)blockIdx.x * pitch4;
+    const int qrow = blockIdx.x / parts, part = blockIdx.x - qrow * parts;
+    const int k_begin = (int)((long long)nsv * part / parts), k_end = (int)((long long)nsv * (part + 1) / parts);
+    const Vec *xq = reinterpret_cast<const Vec *>(Xq) + (size_t)qrow * pitch4;
+    double *dst = parts == 1 ? kbuf : kprod + (size_t)qrow * nsv;
     Vec qv[Q];
 #pragma unroll
     for (int i = 0; i < Q; ++i) {
@@ -246,22 +255,49 @@ decision_rows_kernel(const void *__restrict__ Xq, const void *__restrict__ SV, c
             if (i * 32 + lane < pitch4) accum_pair<CH>(qv[i], qv[i], qn);
         qn = warp_sum_butterfly(qn);
     }
-    for (int k = warp; k < nsv; k += DROWS_THREADS / 32) {
+    for (int k = k_begin + warp; k < k_end; k += (TWO ? 2 : 1) * W) {
+        const int k2 = k + W;
+        const bool second = TWO && k2 < k_end;
         const Vec *row = reinterpret_cast<const Vec *>(SV) + (size_t)k * pitch4;
-        double acc = 0.0;
+        const Vec *row2 = reinterpret_cast<const Vec *>(SV) + (size_t)(second ? k2 : k) * pitch4;
+        Vec r1[Q], r2[TWO ? Q : 1];
 #pragma unroll
         for (int i = 0; i < Q; ++i) {
             const int q = i * 32 + lane;
-            if (q < pitch4) accum_pair<CH>(__ldg(row + q), qv[i], acc);
+            r1[i] = q < pitch4 ? __ldg(row + q) : vec_zero<Vec>();
+            if (TWO) r2[i] = q < pitch4 ? __ldg(row2 + q) : vec_zero<Vec>();
         }
-        acc = warp_sum_butterfly(acc);
-        if (lane == 0) kbuf[k] = svm_exp(-gamma * dist2<XT>(qn, sizeof(XT) == 4 ? svn[k] : 0.0, acc));
+        double acc = 0.0, acc2 = 0.0;
+#pragma unroll
+        for (int i = 0; i < Q; ++i)
+            if (i * 32 + lane < pitch4) accum_pair<CH>(r1[i], qv[i], acc);
+        if (TWO) {
+#pragma unroll
+            for (int i = 0; i < Q; ++i)
+                if (i * 32 + lane < pitch4) accum_pair<CH>(r2[i], qv[i], acc2);
+            warp_sum_butterfly2(acc, acc2, lane);
+        } else {
+            acc = warp_sum_butterfly(acc);
+        }
+        if (lane == 0) {
+            dst[k] = coef[k] * svm_exp(-gamma * dist2<XT>(qn, sizeof(XT) == 4 ? svn[k] : 0.0, acc));
+            if (second) dst[k2] = coef[k2] * svm_exp(-gamma * dist2<XT>(qn, svn[k2], acc2));
+        }
+    }
+    if (parts > 1) {
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) is_last = atomicAdd(done + qrow, 1) == parts - 1;
+        __syncthreads();
+        if (!is_last) return;
+        __threadfence();
+        for (int k = threadIdx.x; k < nsv; k += DROWS_THREADS) kbuf[k] = __ldcg(dst + k);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         double sum = init;
-        for (int k = 0; k < nsv; ++k) sum = sum + coef[k] * kbuf[k];
-        out[blockIdx.x] = sum;
+        for (int k = 0; k < nsv; ++k) sum = sum + kbuf[k];
+        out[qrow] = sum;
     }
 }
 

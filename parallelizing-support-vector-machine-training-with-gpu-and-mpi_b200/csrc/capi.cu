@@ -478,17 +478,29 @@ static cudaError_t launch_decision_any(KernelKey k, const void *Xq, long long m,
     });
 }
 
-// few query rows: one CTA per row (falls back to the streaming kernel when the kernel values do not fit in shared memory)
+// few query rows: a handful of CTAs per row (falls back to the streaming kernel when the kernel values do not fit in
+// shared memory).  rows_work: decision_rows_work_bytes(rows, nsv) of device memory, or NULL = one CTA per row.
+static int decision_rows_parts(int rows, int num_sms) { return std::max(1, std::min(8, num_sms / std::max(rows, 1))); }
+static size_t decision_rows_work_bytes(int rows, int nsv) { return ((size_t)rows * nsv * sizeof(double) + 255 & ~(size_t)255) + (size_t)rows * sizeof(int); }
+
 static cudaError_t launch_decision_rows_any(KernelKey k, const void *Xq, int rows, const void *SV, const double *svn, const double *coef,
-                                            int nsv, int pitch4, double gamma, double init, double *out, int max_smem, cudaStream_t stream)
+                                            int nsv, int pitch4, double gamma, double init, double *out, int max_smem, int num_sms,
+                                            void *rows_work, cudaStream_t stream)
 {
     const size_t smem = (size_t)nsv * sizeof(double) + 16;
     if (smem > (size_t)max_smem) return launch_decision_any(k, Xq, rows, SV, svn, coef, nsv, pitch4, gamma, init, nullptr, out, stream);
+    const int parts = rows_work ? decision_rows_parts(rows, num_sms) : 1;
+    double *kprod = static_cast<double *>(rows_work);
+    int *done = rows_work ? reinterpret_cast<int *>(static_cast<char *>(rows_work) + ((size_t)rows * nsv * sizeof(double) + 255 & ~(size_t)255)) : nullptr;
+    if (parts > 1) {
+        cudaError_t e = cudaMemsetAsync(done, 0, (size_t)rows * sizeof(int), stream);
+        if (e != cudaSuccess) return e;
+    }
     k.threads = k.f64 ? 384 : 512;
     return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(decision_rows_kernel<XT, Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        decision_rows_kernel<XT, Q, CH><<<rows, DROWS_THREADS, smem, stream>>>(Xq, SV, svn, coef, nsv, pitch4, gamma, init, out);
+        decision_rows_kernel<XT, Q, CH><<<rows * parts, DROWS_THREADS, smem, stream>>>(Xq, SV, svn, coef, nsv, pitch4, gamma, init, out, parts, kprod, done);
         return cudaGetLastError();
     });
 }
@@ -903,29 +915,28 @@ extern "C" int svmb200_set_tensor_cores(svmb200_ctx *ctx, int32_t enable, double
     return SVMB200_OK;
 }
 
-// tensor-core scores of m query rows against the current model's support-vector block.  Default: operands packed once
-// (tc_pack_kernel) and streamed by bulk copies through the warp-specialised kernel; SVMB200_TC_KERNEL=staged selects
-// the earlier kernel that splits and stages tiles itself.
+// tensor-core scores of m query rows against a support-vector block: operands packed once (tc_pack_kernel) and streamed
+// by bulk copies through the warp-specialised kernel
 static size_t tc_panel_bytes(const svmb200_ctx *ctx, long long rows)
 {
     return (size_t)((rows + TC_M - 1) / TC_M) * ((ctx->d + TC_KB - 1) / TC_KB) * TCP_PANEL_BYTES;
 }
 
-// qP: tc_panel_bytes(m) of device memory for the packed query rows.  svP: packed support vectors, or NULL = the current
-// model's (ctx->svX), packed once per model and kept.
-static int launch_tc_scores(svmb200_ctx *ctx, const float *Xq, const double *qn, long long m, unsigned char *qP, const float *svX,
-                            const double *svn, const double *svcoef, int nsv, unsigned char *svP, double init, double *dscores, float *dots)
+static size_t tc_partial_bytes(const svmb200_ctx *ctx, long long m, int nsv)
+{
+    int ctas = 0, slots = 0;
+    const long long qtiles = (m + TC_M - 1) / TC_M;
+    tcp_plan(qtiles, (nsv + TC_N - 1) / TC_N, ctx->num_sms, &ctas, &slots);
+    return (size_t)slots * qtiles * TC_M * sizeof(double);
+}
+
+// qP: tc_panel_bytes(m) of device memory for the packed query rows; partial: tc_partial_bytes(m, nsv).  svP: packed support
+// vectors, or NULL = the current model's (ctx->svX), packed once per model and kept.
+static int launch_tc_scores(svmb200_ctx *ctx, const float *Xq, const double *qn, long long m, unsigned char *qP, double *partial,
+                            const float *svX, const double *svn, const double *svcoef, int nsv, unsigned char *svP, double init,
+                            double *dscores, float *dots)
 {
     const int pitch = ctx->pitch4 * 4;
-    const char *which = getenv("SVMB200_TC_KERNEL");
-    if (which && !strcmp(which, "staged")) {
-        CK(cudaFuncSetAttribute(decision_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_smem_bytes()));
-        decision_tc_kernel<<<(unsigned)((m + TC_M - 1) / TC_M), TC_THREADS, decision_tc_smem_bytes(), ctx->stream>>>(
-            Xq, qn, m, svX, svn, svcoef, nsv, pitch, ctx->d, ctx->params.gamma, init, dscores, dots);
-        ctx->launches += 1;
-        CK(cudaGetLastError());
-        return 0;
-    }
     const int kblocks = (ctx->d + TC_KB - 1) / TC_KB;
     const int blocks = ctx->num_sms * 8;
     if (!svP) {
@@ -949,9 +960,15 @@ static int launch_tc_scores(svmb200_ctx *ctx, const float *Xq, const double *qn,
     }
     tc_pack_kernel<<<blocks, 256, 0, ctx->stream>>>(Xq, m, pitch, ctx->d, kblocks, qP);
     CK(cudaGetLastError());
+    int ctas = 0, slots = 0;
+    const long long qtiles = (m + TC_M - 1) / TC_M, mpad = qtiles * TC_M;
+    tcp_plan(qtiles, (nsv + TC_N - 1) / TC_N, ctx->num_sms, &ctas, &slots);
+    CK(cudaMemsetAsync(partial, 0, (size_t)slots * mpad * sizeof(double), ctx->stream));
     CK(cudaFuncSetAttribute(decision_tc_pipelined_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)decision_tc_pipelined_smem_bytes()));
-    decision_tc_pipelined_kernel<<<(unsigned)((m + TC_M - 1) / TC_M), TCP_THREADS, decision_tc_pipelined_smem_bytes(), ctx->stream>>>(
-        qP, qn, m, svP, svn, svcoef, nsv, kblocks, ctx->params.gamma, init, dscores, dots);
+    decision_tc_pipelined_kernel<<<ctas, TCP_THREADS, decision_tc_pipelined_smem_bytes(), ctx->stream>>>(
+        qP, qn, m, svP, svn, svcoef, nsv, kblocks, ctx->params.gamma, partial, mpad, dots);
+    tc_sum_partials_kernel<<<(unsigned)((m + 255) / 256), 256, 0, ctx->stream>>>(partial, slots, mpad, m, init, dscores);
+    ctx->launches += 1;
     ctx->launches += 2;
     CK(cudaGetLastError());
     return 0;
@@ -969,13 +986,14 @@ extern "C" int svmb200_debug_tc_dots(svmb200_ctx *ctx, float *dots, int64_t *rec
     const long long rows = std::min<long long>(ctx->n, TC_M);
     if (int rc = ensure_norms(ctx, DEFAULT_CHUNK)) return rc;
     const size_t head = (size_t)TC_M * TC_N * sizeof(float) + (size_t)TC_M * 2 * sizeof(double), panel = tc_panel_bytes(ctx, rows);
-    if (int rc = ensure_work(ctx, 0, head + 2 * panel)) return rc;
+    const size_t part = tc_partial_bytes(ctx, rows, (int)rows);
+    if (int rc = ensure_work(ctx, 0, head + 2 * panel + part)) return rc;
     float *d_dots = static_cast<float *>(ctx->work[0]);
     double *coef = reinterpret_cast<double *>(d_dots + TC_M * TC_N), *out = coef + TC_M;
     unsigned char *qP = static_cast<unsigned char *>(ctx->work[0]) + head;
     CK(cudaMemsetAsync(ctx->work[0], 0, head, ctx->stream));
-    if (int rc = launch_tc_scores(ctx, static_cast<const float *>(ctx->X), ctx->sqn, rows, qP, static_cast<const float *>(ctx->X), ctx->sqn, coef,
-                                  (int)rows, qP + panel, 0.0, out, d_dots))
+    if (int rc = launch_tc_scores(ctx, static_cast<const float *>(ctx->X), ctx->sqn, rows, qP, reinterpret_cast<double *>(qP + 2 * panel),
+                                  static_cast<const float *>(ctx->X), ctx->sqn, coef, (int)rows, qP + panel, 0.0, out, d_dots))
         return rc;
     CK(cudaMemcpyAsync(dots, d_dots, (size_t)TC_M * TC_N * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -1029,7 +1047,8 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     const bool use_tc = ctx->tc_predict && !ctx->x_f64 && ctx->model_nsv > 0;
     const size_t o_x = 0, o_scores = o_x + up((size_t)m * pitch4 * 16), o_y = o_scores + up((size_t)m * sizeof(double)),
                  o_qn = o_y + up(((size_t)m + 1) * sizeof(int)), o_list = o_qn + (use_tc ? up((size_t)m * sizeof(double)) : 0),
-                 o_panel = o_list + (use_tc ? up(((size_t)m + 1) * sizeof(int)) : 0), o_end = o_panel + (use_tc ? tc_panel_bytes(ctx, m) : 0);
+                 o_panel = o_list + (use_tc ? up(((size_t)m + 1) * sizeof(int)) : 0), o_part = o_panel + (use_tc ? tc_panel_bytes(ctx, m) : 0),
+                 o_end = o_part + (use_tc ? tc_partial_bytes(ctx, m, ctx->model_nsv) : 0);
     if (int rc = ensure_work(ctx, 0, o_end)) return rc;
     char *w = static_cast<char *>(ctx->work[0]);
     void *Xq = w + o_x;
@@ -1044,7 +1063,7 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
         int *list = reinterpret_cast<int *>(w + o_list);
         CK(launch_sqnorm_any(key, static_cast<const float *>(Xq), m, pitch4, qn, ctx->stream));
         if (int rc = launch_tc_scores(ctx, static_cast<const float *>(Xq), qn, m, reinterpret_cast<unsigned char *>(w + o_panel),
-                                      static_cast<const float *>(ctx->svX), ctx->svn, ctx->svcoef, nsv, nullptr, -ctx->b, dscores, nullptr))
+                                      reinterpret_cast<double *>(w + o_part), static_cast<const float *>(ctx->svX), ctx->svn, ctx->svcoef, nsv, nullptr, -ctx->b, dscores, nullptr))
             return rc;
         int n_unc = 0;
         CK(cudaMemsetAsync(list + m, 0, sizeof(int), ctx->stream));
@@ -1054,16 +1073,17 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
         CK(cudaStreamSynchronize(ctx->stream));
         ctx->launches += 2;
         if (n_unc > 0) {
-            const size_t xu_bytes = up((size_t)n_unc * pitch4 * 16);
-            if (int rc = ensure_work(ctx, 1, xu_bytes + (size_t)n_unc * sizeof(double))) return rc;
+            const size_t xu_bytes = up((size_t)n_unc * pitch4 * 16), ex_bytes = up((size_t)n_unc * sizeof(double));
+            if (int rc = ensure_work(ctx, 1, xu_bytes + ex_bytes + decision_rows_work_bytes(n_unc, nsv))) return rc;
             void *Xu = ctx->work[1];
             double *exact = reinterpret_cast<double *>(static_cast<char *>(ctx->work[1]) + xu_bytes);
+            void *rows_work = static_cast<char *>(ctx->work[1]) + xu_bytes + ex_bytes;
             const long long total = (long long)n_unc * pitch4;
             gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
                 Xq, nullptr, pitch4, list, n_unc, Xu, qn /* norms unused by the exact kernel: scratch */);
             CK(cudaGetLastError());
             CK(launch_decision_rows_any(key, Xu, n_unc, ctx->svX, ctx->svn, ctx->svcoef, nsv, pitch4, ctx->params.gamma, -ctx->b, exact,
-                                        ctx->max_smem_optin, ctx->stream));
+                                        ctx->max_smem_optin, ctx->num_sms, rows_work, ctx->stream));
             scatter_scores_kernel<<<(n_unc + 255) / 256, 256, 0, ctx->stream>>>(exact, list, n_unc, dscores);
             CK(cudaGetLastError());
             ctx->launches += 3;

@@ -477,4 +477,15 @@ def test_tensor_core_predict_equals_exact_labels(solver, O, dataset):
     unc = np.abs(s_tc) < 0.05
     assert np.array_equal(s_tc[unc], s_exact[unc])                # rows under the threshold were re-evaluated exactly
     assert 0 <= rechecked <= m // 4
+    # a threshold above every |score|: all rows go through the re-evaluation (one CTA per row instead of several) and
+    # every score is the exact kernel's, bit for bit; then a batch of ONE row (a single pair of tiles)
+    try:
+        solver.set_tensor_cores(True, 1e3)
+        c_all, s_all = solver.predict_u8(Xt, yt)
+        assert solver.tc_rechecked() == m
+        c_one, s_one = solver.predict_u8(Xt[:1], yt[:1])
+    finally:
+        solver.set_tensor_cores(False)
+    assert c_all == c_exact and np.array_equal(s_all, s_exact)
+    assert np.array_equal(s_one, s_exact[:1])
     print(f"tensor-core predict: max |score error| {np.max(np.abs(s_tc - s_exact)):.2e}, {rechecked} of {m} rows re-evaluated")
