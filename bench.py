@@ -281,7 +281,7 @@ def run_ours(args):
     alg_bytes = args.n * row_bytes                                # per GPU per iteration: X once
     achieved = alg_bytes / (ms_per_step * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "smo_persistent_kernel<7,4,512>",
+                "traffic": None, "peak_source": peak_src, "kernel": "smo_persistent_kernel<float,7,4,384>",
                 "algorithmic_bytes_per_iteration": alg_bytes,
                 "note": "per GPU; one launch runs all K iterations: achieved = K * N*784*4 / kernel time (CUDA events)"}
     prof = os.path.join(ROOT, "profiles", "traffic.json")

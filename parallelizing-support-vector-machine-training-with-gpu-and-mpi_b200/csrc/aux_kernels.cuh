@@ -133,11 +133,13 @@ __global__ void gather_rows_kernel(const void *__restrict__ X, const double *__r
 // warm-start f rebuild (code/mpi_svm_main2.cpp:169-183).
 //   out[i] = init + sum_k coef[k] * K(q_i, sv_k)   (k ascending, sequential FP64, as the reference)
 //   then, if ysub != nullptr, out[i] -= ysub[i]     (f_i = sum - y_i)
-// A warp owns one query row (registers); the CTA streams the support-vector block through shared
-// memory in tiles of DEC_TILE rows (bulk copies, double-buffered), every warp reading each tile.
+// A warp owns one or two query rows (registers: two when the rows are fp32, so that every support-vector row read
+// from shared memory serves two dot products); the CTA streams the support-vector block through shared memory in
+// tiles of DEC_TILE rows (bulk copies, double-buffered), every warp reading each tile.
 constexpr int DEC_THREADS = 512;
 constexpr int DEC_WARPS = DEC_THREADS / 32;
 constexpr int DEC_TILE = 16;
+template <typename XT, int Q> constexpr int dec_rows_per_warp() { return (sizeof(XT) == 4 && Q <= 8) ? 2 : 1; }
 
 template <typename XT, int Q, int CH>
 __global__ void __launch_bounds__(DEC_THREADS, 1)
@@ -145,6 +147,7 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
                 const double *__restrict__ coef, int nsv, int pitch4, double gamma, double init, const int *__restrict__ ysub, double *__restrict__ out)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int QR = dec_rows_per_warp<XT, Q>();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row_bytes = pitch4 * 16;
     unsigned char *tiles = smem_raw;                                   // [2][DEC_TILE][row_bytes]
@@ -158,20 +161,24 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
     __syncthreads();
 
     using Vec = typename RowVec<XT>::type;
-    const long long qi = (long long)blockIdx.x * DEC_WARPS + warp;
-    const bool active = qi < m;
-    Vec qv[Q];
+    const long long qi0 = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * QR;     // the host picks the CTA size (<= DEC_THREADS)
+    Vec qv[QR][Q];
+    double qn[QR];                                                     // |q|^2, the same way the solver forms norms (fp32 rows)
 #pragma unroll
-    for (int i = 0; i < Q; ++i) {
-        const int q = i * 32 + lane;
-        qv[i] = (active && q < pitch4) ? __ldg(reinterpret_cast<const Vec *>(Xq) + (size_t)qi * pitch4 + q) : vec_zero<Vec>();
-    }
-    double qn = 0.0;                                                   // |q|^2, the same way the solver forms norms (fp32 rows)
-    if (sizeof(XT) == 4) {
+    for (int u = 0; u < QR; ++u) {
+        const bool active = qi0 + u < m;
 #pragma unroll
-        for (int i = 0; i < Q; ++i)
-            if (i * 32 + lane < pitch4) accum_pair<CH>(qv[i], qv[i], qn);
-        qn = warp_sum_butterfly(qn);
+        for (int i = 0; i < Q; ++i) {
+            const int q = i * 32 + lane;
+            qv[u][i] = (active && q < pitch4) ? __ldg(reinterpret_cast<const Vec *>(Xq) + (size_t)(qi0 + u) * pitch4 + q) : vec_zero<Vec>();
+        }
+        qn[u] = 0.0;
+        if (sizeof(XT) == 4) {
+#pragma unroll
+            for (int i = 0; i < Q; ++i)
+                if (i * 32 + lane < pitch4) accum_pair<CH>(qv[u][i], qv[u][i], qn[u]);
+            qn[u] = warp_sum_butterfly(qn[u]);
+        }
     }
 
     const int ntiles = (nsv + DEC_TILE - 1) / DEC_TILE;
@@ -183,38 +190,113 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
     };
     if (threadIdx.x == 0 && ntiles > 0) issue_tile(0);
 
-    double sum = init;
-    for (int t = 0; t < ntiles; ++t) {
-        if (threadIdx.x == 0 && t + 1 < ntiles) issue_tile(t + 1);   // buffer (t+1)&1 was released by the barrier below
-        mbar_wait(&bars[t & 1], (t >> 1) & 1);
-        const int rows = min(DEC_TILE, nsv - t * DEC_TILE);
-        const unsigned char *tile = tiles + (size_t)(t & 1) * DEC_TILE * row_bytes;
-        double myk = 0.0;
-        for (int r = 0; r < rows; ++r) {
-            const Vec *row = reinterpret_cast<const Vec *>(tile + (size_t)r * row_bytes);
-            double acc = 0.0;
+    if constexpr (QR == 2) {
+        // Two query rows x 8 support-vector rows = 16 dot products at a time.  Every lane first forms its partial sum of
+        // each (the lane's 16-byte groups, in order, exactly as everywhere else); the 16 warp sums are then formed by a
+        // halving exchange: at offset 16 a lane keeps the 8 sums of "its" query row and sends the other 8, at offsets
+        // 8, 4, 2 it keeps half of what it has, at offset 1 it adds.  Each addition pairs the same two operands as the
+        // plain xor butterfly (which leaves the same bits in every lane), so lane l ends up holding the butterfly's
+        // value for query row l >> 4 and support-vector row (l >> 1) & 7 -- with 16 shuffles per 16 sums instead of 80.
+        double *prodbuf = reinterpret_cast<double *>(bars + 2) + warp * 16;      // [query row][8] products of the half tile
+        const int my_u = lane >> 4, my_r = (lane >> 1) & 7;
+        const double my_qn = my_u ? qn[QR - 1] : qn[0];
+        double sum = init;                                                      // lanes 0-15: query row 0, lanes 16-31: query row 1
+        for (int t = 0; t < ntiles; ++t) {
+            if (threadIdx.x == 0 && t + 1 < ntiles) issue_tile(t + 1);   // buffer (t+1)&1 was released by the barrier below
+            mbar_wait(&bars[t & 1], (t >> 1) & 1);
+            const int rows = min(DEC_TILE, nsv - t * DEC_TILE);
+            const unsigned char *tile = tiles + (size_t)(t & 1) * DEC_TILE * row_bytes;
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                const int rows_here = min(8, rows - half * 8);
+                if (rows_here <= 0) break;
+                double P[16];                                                   // [u * 8 + r]
 #pragma unroll
-            for (int i = 0; i < Q; ++i) {
-                const int q = i * 32 + lane;
-                if (q < pitch4) accum_pair<CH>(row[q], qv[i], acc);
+                for (int j = 0; j < 16; ++j) P[j] = 0.0;
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    const Vec *row = reinterpret_cast<const Vec *>(tile + (size_t)(half * 8 + r) * row_bytes);
+#pragma unroll
+                    for (int i = 0; i < Q; ++i) {
+                        // no per-lane test: the query registers are zero beyond the row, so a (clamped, hence finite) element
+                        // read there adds +-0 to the lane's sum; only groups wholly beyond the row are skipped (warp-uniform)
+                        if (i * 32 < pitch4) {
+                            const Vec sv = row[min(i * 32 + lane, pitch4 - 1)];
+                            accum_pair<CH>(sv, qv[0][i], P[r]);
+                            accum_pair<CH>(sv, qv[QR - 1][i], P[8 + r]);
+                        }
+                    }
+                }
+                double v8[8], v4[4], v2[2], v1;
+                {
+                    const bool up = (lane & 16) != 0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v8[j] = (up ? P[8 + j] : P[j]) + __shfl_xor_sync(FULL, up ? P[j] : P[8 + j], 16);
+                }
+                {
+                    const bool up = (lane & 8) != 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) v4[j] = (up ? v8[4 + j] : v8[j]) + __shfl_xor_sync(FULL, up ? v8[j] : v8[4 + j], 8);
+                }
+                {
+                    const bool up = (lane & 4) != 0;
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) v2[j] = (up ? v4[2 + j] : v4[j]) + __shfl_xor_sync(FULL, up ? v4[j] : v4[2 + j], 4);
+                }
+                {
+                    const bool up = (lane & 2) != 0;
+                    v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 2);
+                }
+                v1 = v1 + __shfl_xor_sync(FULL, v1, 1);
+                const int k_mine = t * DEC_TILE + half * 8 + my_r;
+                const bool valid = my_r < rows_here;
+                const double kv = svm_exp(-gamma * dist2<XT>(my_qn, valid ? svn[k_mine] : 0.0, v1));
+                __syncwarp();                                                   // the previous half's products have been read
+                if (valid && !(lane & 1)) prodbuf[my_u * 8 + my_r] = coef[k_mine] * kv;
+                __syncwarp();
+                for (int r = 0; r < rows_here; ++r) sum = sum + prodbuf[my_u * 8 + r];   // curr += alpha[j]*y[j] * kernel(...), k ascending
             }
-            acc = warp_sum_butterfly(acc);
-            if (lane == r) myk = acc;
+            fence_proxy_async();
+            __syncthreads();                                              // everyone is done with buffer t&1
         }
-        const double myn = (sizeof(XT) == 4 && lane < rows) ? svn[t * DEC_TILE + lane] : 0.0;
-        myk = svm_exp(-gamma * dist2<XT>(qn, myn, myk));        // lanes >= rows compute a value nobody reads
-        const double mycoef = lane < rows ? coef[t * DEC_TILE + lane] : 0.0;
-        for (int r = 0; r < rows; ++r) {
-            const double k = __shfl_sync(FULL, myk, r);
-            const double c = __shfl_sync(FULL, mycoef, r);
-            sum = sum + c * k;                                        // curr += alpha[j]*y[j] * kernel(...)
+        if ((lane & 15) == 0 && qi0 + my_u < m) {
+            if (ysub) sum = sum - (double)ysub[qi0 + my_u];
+            out[qi0 + my_u] = sum;
         }
-        fence_proxy_async();
-        __syncthreads();                                              // everyone is done with buffer t&1
-    }
-    if (active && lane == 0) {
-        if (ysub) sum = sum - (double)ysub[qi];
-        out[qi] = sum;
+    } else {
+        double sum = init;
+        for (int t = 0; t < ntiles; ++t) {
+            if (threadIdx.x == 0 && t + 1 < ntiles) issue_tile(t + 1);   // buffer (t+1)&1 was released by the barrier below
+            mbar_wait(&bars[t & 1], (t >> 1) & 1);
+            const int rows = min(DEC_TILE, nsv - t * DEC_TILE);
+            const unsigned char *tile = tiles + (size_t)(t & 1) * DEC_TILE * row_bytes;
+            double myk = 0.0;
+            for (int r = 0; r < rows; ++r) {
+                const Vec *row = reinterpret_cast<const Vec *>(tile + (size_t)r * row_bytes);
+                double acc = 0.0;
+#pragma unroll
+                for (int i = 0; i < Q; ++i) {
+                    const int q = i * 32 + lane;
+                    if (q < pitch4) accum_pair<CH>(row[q], qv[0][i], acc);
+                }
+                acc = warp_sum_butterfly(acc);
+                if (lane == r) myk = acc;
+            }
+            const double myn = (sizeof(XT) == 4 && lane < rows) ? svn[t * DEC_TILE + lane] : 0.0;
+            myk = svm_exp(-gamma * dist2<XT>(qn[0], myn, myk));        // lanes >= rows compute a value nobody reads
+            const double mycoef = lane < rows ? coef[t * DEC_TILE + lane] : 0.0;
+            for (int r = 0; r < rows; ++r) {
+                const double k = __shfl_sync(FULL, myk, r);
+                const double c = __shfl_sync(FULL, mycoef, r);
+                sum = sum + c * k;                                        // curr += alpha[j]*y[j] * kernel(...)
+            }
+            fence_proxy_async();
+            __syncthreads();                                              // everyone is done with buffer t&1
+        }
+        if (lane == 0 && qi0 < m) {
+            if (ysub) sum = sum - (double)ysub[qi0];
+            out[qi0] = sum;
+        }
     }
 }
 
@@ -301,7 +383,7 @@ decision_rows_kernel(const void *__restrict__ Xq, const void *__restrict__ SV, c
     }
 }
 
-inline size_t decision_smem_bytes(int pitch4) { return (size_t)2 * DEC_TILE * pitch4 * 16 + 64; }
+inline size_t decision_smem_bytes(int pitch4) { return (size_t)2 * DEC_TILE * pitch4 * 16 + 16 + (size_t)DEC_WARPS * 16 * sizeof(double); }
 
 // ---- accuracy: replaces the predict/compare/reduce_sum tail (code/main3.cpp:399-401;
 // gpu_svm_main3.cu:291,299-315): "> 0" (serial/GPU) or ">= 0" (MPI programs)
