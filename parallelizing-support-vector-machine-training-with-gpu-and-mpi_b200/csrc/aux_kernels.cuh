@@ -136,12 +136,13 @@ __global__ void gather_rows_kernel(const void *__restrict__ X, const double *__r
 // A warp owns one or two query rows (registers: two when the rows are fp32, so that every support-vector row read
 // from shared memory serves two dot products); the CTA streams the support-vector block through shared memory in
 // tiles of DEC_TILE rows (bulk copies, double-buffered), every warp reading each tile.
-constexpr int DEC_THREADS = 512;
+constexpr int DEC_THREADS = 384;     // 12 warps: up to 168 registers each, room to keep the loads of several rows in flight
 constexpr int DEC_WARPS = DEC_THREADS / 32;
 constexpr int DEC_TILE = 16;
 template <typename XT, int Q> constexpr int dec_rows_per_warp() { return (sizeof(XT) == 4 && Q <= 8) ? 2 : 1; }
 
-template <typename XT, int Q, int CH>
+// FULL: every one of the Q register groups reaches into the row ((Q - 1) * 32 < pitch4), so the fp32 loop needs no test at all
+template <typename XT, int Q, int CH, bool FULL>
 __global__ void __launch_bounds__(DEC_THREADS, 1)
 decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict__ SV, const double *__restrict__ svn,
                 const double *__restrict__ coef, int nsv, int pitch4, double gamma, double init, const int *__restrict__ ysub, double *__restrict__ out)
@@ -199,6 +200,9 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
         // value for query row l >> 4 and support-vector row (l >> 1) & 7 -- with 16 shuffles per 16 sums instead of 80.
         double *prodbuf = reinterpret_cast<double *>(bars + 2) + warp * 16;      // [query row][8] products of the half tile
         const int my_u = lane >> 4, my_r = (lane >> 1) & 7;
+        int qoff[Q];                                                            // this lane's 16-byte group of each register group, clamped into the row
+#pragma unroll
+        for (int i = 0; i < Q; ++i) qoff[i] = min(i * 32 + lane, pitch4 - 1);
         const double my_qn = my_u ? qn[QR - 1] : qn[0];
         double sum = init;                                                      // lanes 0-15: query row 0, lanes 16-31: query row 1
         for (int t = 0; t < ntiles; ++t) {
@@ -220,8 +224,8 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
                     for (int i = 0; i < Q; ++i) {
                         // no per-lane test: the query registers are zero beyond the row, so a (clamped, hence finite) element
                         // read there adds +-0 to the lane's sum; only groups wholly beyond the row are skipped (warp-uniform)
-                        if (i * 32 < pitch4) {
-                            const Vec sv = row[min(i * 32 + lane, pitch4 - 1)];
+                        if (FULL || i * 32 < pitch4) {
+                            const Vec sv = row[qoff[i]];
                             accum_pair<CH>(sv, qv[0][i], P[r]);
                             accum_pair<CH>(sv, qv[QR - 1][i], P[8 + r]);
                         }

@@ -464,6 +464,28 @@ static cudaError_t launch_smo_any(const KernelKey &k, const SmoArgs &args, int g
     });
 }
 
+template <typename XT, int Q, int CH, bool FULL>
+static cudaError_t launch_decision(const void *Xq, long long m, const void *SV, const double *svn, const double *coef, int nsv, int pitch4,
+                                   double gamma, double init, const int *ysub, double *out, int num_sms, cudaStream_t stream)
+{
+    const size_t smem = decision_smem_bytes(pitch4);
+    cudaError_t e = cudaFuncSetAttribute(decision_kernel<XT, Q, CH, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    // every CTA streams the whole support-vector block, so a launch costs (waves of CTAs) x (warps per CTA): pick the
+    // CTA size between 8 and DEC_WARPS warps that wastes least of the last wave
+    constexpr int per_warp = dec_rows_per_warp<XT, Q>();
+    int warps = DEC_WARPS;
+    long long best_cost = -1;
+    for (int w = DEC_WARPS; w >= 8; --w) {
+        const long long ctas = (m + (long long)w * per_warp - 1) / ((long long)w * per_warp);
+        const long long cost = ((ctas + num_sms - 1) / num_sms) * w;
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; warps = w; }
+    }
+    const int grid = (int)((m + (long long)warps * per_warp - 1) / ((long long)warps * per_warp));
+    decision_kernel<XT, Q, CH, FULL><<<grid, warps * 32, smem, stream>>>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out);
+    return cudaGetLastError();
+}
+
 static cudaError_t launch_decision_any(KernelKey k, const void *Xq, long long m, const void *SV, const double *svn, const double *coef,
                                        int nsv, int pitch4, double gamma, double init, const int *ysub, double *out, cudaStream_t stream)
 {
@@ -471,22 +493,9 @@ static cudaError_t launch_decision_any(KernelKey k, const void *Xq, long long m,
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     k.threads = k.f64 ? 384 : 512;      // one instantiation per (XT, Q, CH): the CTA size of this kernel is fixed
     return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
-        const size_t smem = decision_smem_bytes(pitch4);
-        cudaError_t e = cudaFuncSetAttribute(decision_kernel<XT, Q, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        // every CTA streams the whole support-vector block, so a launch costs (waves of CTAs) x (warps per CTA): pick the
-        // CTA size between 8 and 16 warps that wastes least of the last wave
-        constexpr int per_warp = dec_rows_per_warp<XT, Q>();
-        int warps = DEC_WARPS;
-        long long best_cost = -1;
-        for (int w = DEC_WARPS; w >= 8; --w) {
-            const long long ctas = (m + (long long)w * per_warp - 1) / ((long long)w * per_warp);
-            const long long cost = ((ctas + num_sms - 1) / num_sms) * w;
-            if (best_cost < 0 || cost < best_cost) { best_cost = cost; warps = w; }
-        }
-        const int grid = (int)((m + (long long)warps * per_warp - 1) / ((long long)warps * per_warp));
-        decision_kernel<XT, Q, CH><<<grid, warps * 32, smem, stream>>>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out);
-        return cudaGetLastError();
+        if (sizeof(XT) == 4 && (Q - 1) * 32 < pitch4)
+            return launch_decision<XT, Q, CH, true>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, num_sms, stream);
+        return launch_decision<XT, Q, CH, false>(Xq, m, SV, svn, coef, nsv, pitch4, gamma, init, ysub, out, num_sms, stream);
     });
 }
 
