@@ -222,6 +222,11 @@ def test_predict_matches_oracle(solver, O, dataset):
     assert c_ge == O.predict(xt, yt, xs, y, out["alpha"], out["b"], ge_zero=True, arith=O.ARITH_DEVICE)[0]
     c_f64, s_f64 = solver.predict_f64(Xt.astype(np.float64), yt)
     assert c_f64 == c_gpu and np.array_equal(s_f64, s_gpu)
+    # a row's score does not depend on the batch it arrives in (ragged batches: 1, 33 and 383 rows; the kernel takes two
+    # query rows per warp and picks its CTA size per launch)
+    for k in (1, 33, 383):
+        _, s_part = solver.predict_u8(Xt[:k], yt[:k])
+        assert np.array_equal(s_part, s_gpu[:k]), k
 
 
 def test_model_save_and_load(solver, pkg, dataset, tmp_path):
