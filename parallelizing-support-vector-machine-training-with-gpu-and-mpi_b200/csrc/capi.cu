@@ -171,7 +171,7 @@ void svmb200_default_params(svmb200_params *p)
     p->cache_rows = 0;
     p->accum_chunk = 0;
     p->trace_cap = 0;
-    p->l2_persist = 0;
+    p->l2_persist = -1;
     p->keep_cache = 0;
 }
 
@@ -446,6 +446,7 @@ static cudaError_t dispatch(const KernelKey &k, F &&fn)
     case 2: SVM_F32_CASE(2, 512)
     case 4: SVM_F32_CASE(4, 512)
     case 7:
+        if (k.threads == 192) { SVM_F32_CASE(7, 192) }
         if (k.threads == 256) { SVM_F32_CASE(7, 256) }
         if (k.threads == 384) { SVM_F32_CASE(7, 384) }
         SVM_F32_CASE(7, 512)
@@ -560,7 +561,9 @@ static int ensure_norms(svmb200_ctx *ctx, int CH)
     return 0;
 }
 
-static const int SMO_DEFAULT_THREADS_Q7 = 384;   // 12 warps, 164 registers each, no spills: 33.4 us/iteration at 60k against 35.4 with 512 threads
+// 8 warps x four rows per step (242 registers, no spills) + L2-resident share of X: 25.9 us/iteration at 60k; 12 warps x one row per
+// step (165 registers): 33.4; 16 warps (128 registers, spills): 35.4
+static const int SMO_DEFAULT_THREADS_Q7 = 256;
 static const int DEFAULT_CHUNK = 4;   // fp32 storage of X dominates the error of K for every chunk (DESIGN.md "Numerics")
 
 static int resolve_chunk(int c)
@@ -617,16 +620,18 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         threads = SMO_DEFAULT_THREADS_Q7;
         if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py
             const int t = atoi(e);
-            if (t == 256 || t == 384 || t == 512) threads = t;
+            if (t == 192 || t == 256 || t == 384 || t == 512) threads = t;
         }
     }
     const int warps = threads / 32;
     // ring depth per warp: 4 rows with the 12-warp CTA of the MNIST shape (12 x 4 x 3136 B = 147 KB per SM in flight), 2 elsewhere
     // (with 16 warps two rows per warp already saturate HBM and deeper rings only lengthen the queues the exchange waits behind)
-    int kslots = (Q == 7 && !ctx->x_f64) ? 4 : 2;
+    // (the 8-warp CTA takes four rows per step: a slot is a group of four rows, one in use + one in flight)
+    const int rps = (Q == 7 && !ctx->x_f64 && threads <= 256) ? 4 : 1;      // = smo_rows_per_step<XT, Q, THREADS>()
+    int kslots = (Q == 7 && !ctx->x_f64) ? (rps == 4 ? (threads == 192 ? 3 : 2) : 4) : 2;
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
-    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps) > (size_t)ctx->max_smem_optin) --kslots;
-    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps);
+    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps) > (size_t)ctx->max_smem_optin) --kslots;
+    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
     const long long n_own = n * (ctx->shard_rank + 1) / ctx->shard_world - n * ctx->shard_rank / ctx->shard_world;
     const int grid = (int)std::max<long long>(1, std::min<long long>(ctx->num_sms, (n_own + 7) / 8));
@@ -697,14 +702,17 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     a.C = params->C; a.gamma = params->gamma; a.eps = params->eps; a.tau = params->tau;
     a.policy_stream = L2_EVICT_FIRST; a.policy_keep = L2_EVICT_LAST; a.keep_per_1024 = 0;
     {
-        // L2 residency: when X does not fit in L2, keep a leading share of every warp's rows
-        const double x_bytes = (double)n * ctx->pitch4 * 16;
-        double l2_keep_budget = 96.0 * 1024 * 1024;
+        // L2 residency: when this GPU's rows do not fit in L2, a share of them (evenly interleaved groups) is loaded with
+        // evict-last and stays resident from one pass to the next; the rest streams with evict-first.  80 MB of the 126 MB
+        // measured best at 60 000 x 784 (25.9 us per iteration; 64 MB 27.3, 88 MB 26.9, 96 MB 28.6, none 35.0).  It pays
+        // only with the four-rows-per-step pass: with a row per step the SM side, not HBM, bounds the pass.
+        const double x_bytes = (double)n_own * ctx->pitch4 * 16;
+        double l2_keep_budget = 80.0 * 1024 * 1024;
         if (const char *e = getenv("SVMB200_L2KEEP_MB")) l2_keep_budget = atof(e) * 1024 * 1024;
         int persist = params->l2_persist;
-        if (persist < 0) persist = 1;
+        if (persist < 0) persist = rps == 4;
         if (x_bytes <= 96.0 * 1024 * 1024) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
-        else if (persist) a.keep_per_1024 = (int)(1024.0 * l2_keep_budget / x_bytes);
+        else if (persist) a.keep_per_1024 = (int)std::min(1024.0, 1024.0 * l2_keep_budget / x_bytes);
     }
     a.peers = ctx->shard_world; a.rank = ctx->shard_rank;
     a.row_begin = n * ctx->shard_rank / ctx->shard_world;

@@ -76,6 +76,12 @@ struct SmoArgs {
     int timing_cap;
 };
 
+// Rows a warp takes per step of the X pass.  1: a row at a time (two sums per butterfly).  4 (fp32 rows, Q = 7, the 8-warp
+// CTA): the ring holds groups of four consecutive rows (one bulk copy, one mbarrier per group); four rows x two pivots =
+// eight sums per halving exchange, eight independent accumulation chains.
+template <typename XT, int Q, int THREADS>
+constexpr int smo_rows_per_step() { return (sizeof(XT) == 4 && Q == 7 && THREADS <= 256) ? 4 : 1; }
+
 // ------------------------------------------------------------------------------------------
 template <typename Vec, int Q>
 struct Pivots {
@@ -380,8 +386,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     // shared-memory carve-up: [warps][slots] rows | mbarriers | Shared
     unsigned char *slots = smem_raw;
     const int KS = a.kslots;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + (size_t)WARPS * KS * row_bytes);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slots + (size_t)WARPS * KS * smo_rows_per_step<XT, Q, THREADS>() * row_bytes);
     Shared &sh = *reinterpret_cast<Shared *>(bars + WARPS * SMO_KSLOTS_MAX);
+    constexpr int RPS = smo_rows_per_step<XT, Q, THREADS>();
+    // (RPS == 4) per warp: the two sums of each of the 32 rows of a block, parked until their lane finishes the rows
+    double2 *stage = reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(&sh) + ((sizeof(Shared) + 15) & ~(size_t)15)) + warp * 32;
 
 
     // rows owned by this CTA and, inside it, by this warp (contiguous ranges)
@@ -389,12 +398,14 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     const long long r0 = a.row_begin + (long long)blockIdx.x * n_own / G;
     const long long r1 = a.row_begin + (long long)(blockIdx.x + 1) * n_own / G;
     const long long R = r1 - r0;
-    const long long w0 = r0 + (long long)warp * R / WARPS;
-    const long long w1 = r0 + (long long)(warp + 1) * R / WARPS;
+    // warps take contiguous ranges, cut at multiples of RPS rows from r0 (so only the CTA's last rows form a short group)
+    const long long units = (R + RPS - 1) / RPS;
+    const long long w0 = min(r1, r0 + RPS * ((long long)warp * units / WARPS));
+    const long long w1 = min(r1, r0 + RPS * ((long long)(warp + 1) * units / WARPS));
     const int m = (int)(w1 - w0);
     const int keep_rows = (int)(((long long)m * a.keep_per_1024) >> 10);
 
-    unsigned char *my_slots = slots + (size_t)warp * KS * row_bytes;
+    unsigned char *my_slots = slots + (size_t)warp * KS * RPS * row_bytes;
     uint64_t *my_bars = bars + warp * SMO_KSLOTS_MAX;
     if (lane == 0) {
         for (int s = 0; s < KS; ++s) mbar_init(&my_bars[s], 1);
@@ -408,12 +419,21 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     unsigned cphase = 0;                 // mbarrier phase parity of that slot
     int pf_row = 0;                      // next row of the range to request
     auto issue_into = [&](int s) {       // called by the whole warp (state stays warp-uniform); lane 0 issues
+        const int nrows = RPS == 1 ? 1 : min(RPS, m - pf_row);       // a slot holds RPS consecutive rows (fewer at the end of the range)
         if (lane == 0) {
-            mbar_expect_tx(&my_bars[s], (unsigned)row_bytes);
-            bulk_g2s(my_slots + (size_t)s * row_bytes, Xb + (size_t)(w0 + pf_row) * row_bytes, (unsigned)row_bytes,
-                     &my_bars[s], pf_row < keep_rows ? a.policy_keep : a.policy_stream);
+            // which rows stay in L2 (policy_keep): with one row per slot the leading share of the warp's range; with groups
+            // an evenly interleaved share, so that L2 hits and HBM reads alternate through the whole pass
+            bool keep = pf_row < keep_rows;
+            if (RPS > 1) {
+                const int g = pf_row / RPS;
+                keep = (((g + 1) * a.keep_per_1024) >> 10) != ((g * a.keep_per_1024) >> 10);
+            }
+            mbar_expect_tx(&my_bars[s], (unsigned)(nrows * row_bytes));
+            bulk_g2s(my_slots + (size_t)s * RPS * row_bytes, Xb + (size_t)(w0 + pf_row) * row_bytes, (unsigned)(nrows * row_bytes),
+                     &my_bars[s], keep ? a.policy_keep : a.policy_stream);
         }
-        if (++pf_row == m) pf_row = 0;
+        pf_row += nrows;
+        if (pf_row >= m) pf_row = 0;
     };
     if (m > 0)
         for (int s = 0; s < KS; ++s) issue_into(s);
@@ -552,6 +572,99 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         if (!use_cache) {
             // ---------------- X pass: a warp per row ----------------
             ++x_passes;
+            if constexpr (RPS == 4) {
+              int qoff[Q];                       // byte offset of this lane's 16-byte group in each register group, clamped into the row
+#pragma unroll
+              for (int i = 0; i < Q; ++i) qoff[i] = min(i * 32 + lane, a.pitch4 - 1) * 16;
+              const bool full_groups = (Q - 1) * 32 < a.pitch4;   // every register group reaches into the row
+              for (int base = 0; base < m; base += 32) {
+                const int cnt = min(32, m - base);
+                const long long j = w0 + base + lane;
+                double fj = 0.0, aj = 0.0;
+                int yj = 0;
+                long long qj = -1;
+                double nj = 0.0;
+                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; nj = a.sqn[j]; if (a.cacheq) qj = a.cacheq[j]; }
+                for (int t = 0; t < cnt; t += 4) {
+                    const int rows_here = min(4, cnt - t);
+                    mbar_wait(&my_bars[cslot], cphase);
+                    const unsigned char *grp = my_slots + (size_t)cslot * 4 * row_bytes;
+                    // the lane's partial sums of rows t..t+3 against both pivots: [pivot * 4 + row].  No per-lane bounds test:
+                    // the pivot registers are zero beyond the row and the index is clamped (such an element adds +-0).
+                    double P[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) P[k] = 0.0;
+                    if (rows_here == 4 && full_groups) {
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+#pragma unroll
+                            for (int i = 0; i < Q; ++i) {
+                                const Vec v = *reinterpret_cast<const Vec *>(grp + (size_t)r * row_bytes + qoff[i]);
+                                accum_pair<CH>(v, pv.h[i], P[r]);
+                                accum_pair<CH>(v, pv.l[i], P[4 + r]);
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            if (r < rows_here) {
+#pragma unroll
+                                for (int i = 0; i < Q; ++i) {
+                                    if (i * 32 < a.pitch4) {
+                                        const Vec v = *reinterpret_cast<const Vec *>(grp + (size_t)r * row_bytes + qoff[i]);
+                                        accum_pair<CH>(v, pv.h[i], P[r]);
+                                        accum_pair<CH>(v, pv.l[i], P[4 + r]);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    // the group's slot is free again: request the next group of the ring into it
+                    __syncwarp();
+                    fence_proxy_async();
+                    issue_into(cslot);
+                    if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
+                    // halving exchange: offset 16 splits by pivot, 8 and 4 by row, 2 and 1 add.  Each addition pairs the same
+                    // operands as the xor butterfly, so lane l ends with the butterfly's value for pivot l >> 4, row (l >> 2) & 3
+                    double v4[4], v2[2], v1;
+                    {
+                        const bool up = (lane & 16) != 0;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) v4[k] = (up ? P[4 + k] : P[k]) + __shfl_xor_sync(FULL, up ? P[k] : P[4 + k], 16);
+                    }
+                    {
+                        const bool up = (lane & 8) != 0;
+#pragma unroll
+                        for (int k = 0; k < 2; ++k) v2[k] = (up ? v4[2 + k] : v4[k]) + __shfl_xor_sync(FULL, up ? v4[k] : v4[2 + k], 8);
+                    }
+                    {
+                        const bool up = (lane & 4) != 0;
+                        v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 4);
+                    }
+                    v1 = v1 + __shfl_xor_sync(FULL, v1, 2);
+                    v1 = v1 + __shfl_xor_sync(FULL, v1, 1);
+                    if ((lane & 3) == 0) {
+                        const int r = (lane >> 2) & 3;
+                        if (r < rows_here) *(reinterpret_cast<double *>(&stage[t + r]) + (lane >> 4)) = v1;
+                    }
+                }
+                __syncwarp();
+                if (lane < cnt) {
+                    const double2 dd = stage[lane];
+                    const double kh = svm_exp(-a.gamma * dist2<XT>(n_h, nj, dd.x));
+                    const double kl = svm_exp(-a.gamma * dist2<XT>(n_l, nj, dd.y));
+                    fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
+                    a.f[j] = fj;
+                    if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
+                    if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
+                    if (slot_h >= 0 && !(hit_h && hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
+                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
+                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
+                    best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                }
+                __syncwarp();                                  // the parked sums have been read: the next block may overwrite them
+              }
+            } else
             for (int base = 0; base < m; base += 32) {
                 const int cnt = min(32, m - base);
                 // lane t finishes row base+t: its state is requested now and used after the group
@@ -628,9 +741,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     }
 }
 
-inline size_t smo_smem_bytes(int pitch4, int kslots, int warps)
+// kslots: ring depth per warp in slots; a slot holds rows_per_step rows
+inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1)
 {
-    return (size_t)warps * kslots * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128;
+    return (size_t)warps * kslots * rows_per_step * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128 +
+           (size_t)warps * 32 * sizeof(double2);                 // + the parked sums of the four-rows-per-step pass
 }
 
 } // namespace svm
