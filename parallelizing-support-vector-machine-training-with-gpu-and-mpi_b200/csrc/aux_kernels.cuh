@@ -225,7 +225,7 @@ decision_kernel(const void *__restrict__ Xq, long long m, const void *__restrict
                         // no per-lane test: the query registers are zero beyond the row, so a (clamped, hence finite) element
                         // read there adds +-0 to the lane's sum; only groups wholly beyond the row are skipped (warp-uniform)
                         if (FULL || i * 32 < pitch4) {
-                            const Vec sv = row[qoff[i]];
+                            const Vec sv = (FULL && i < Q - 1) ? row[i * 32 + lane] : row[qoff[i]];   // constant offsets from one address
                             accum_pair<CH>(sv, qv[0][i], P[r]);
                             accum_pair<CH>(sv, qv[QR - 1][i], P[8 + r]);
                         }

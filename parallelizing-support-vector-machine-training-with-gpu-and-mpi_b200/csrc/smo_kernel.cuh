@@ -597,9 +597,12 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     if (rows_here == 4 && full_groups) {
 #pragma unroll
                         for (int r = 0; r < 4; ++r) {
+                            // one address per row: the groups 0..Q-2 sit at constant offsets from it, only the last is clamped
+                            const unsigned char *rowp = grp + (size_t)r * row_bytes;
+                            const Vec *lanep = reinterpret_cast<const Vec *>(rowp) + lane;
 #pragma unroll
                             for (int i = 0; i < Q; ++i) {
-                                const Vec v = *reinterpret_cast<const Vec *>(grp + (size_t)r * row_bytes + qoff[i]);
+                                const Vec v = i < Q - 1 ? lanep[i * 32] : *reinterpret_cast<const Vec *>(rowp + qoff[Q - 1]);
                                 accum_pair<CH>(v, pv.h[i], P[r]);
                                 accum_pair<CH>(v, pv.l[i], P[4 + r]);
                             }
