@@ -432,7 +432,9 @@ static cudaError_t dispatch(const KernelKey &k, F &&fn)
         case 2: return fn.template operator()<double, 2, 1, 384>();
         case 4: return fn.template operator()<double, 4, 1, 384>();
         case 7: return fn.template operator()<double, 7, 1, 384>();
-        default: return fn.template operator()<double, 13, 1, 384>();
+        default:
+            if (k.threads == 256) return fn.template operator()<double, 13, 1, 256>();   // the SMO kernel's two-rows-per-step form
+            return fn.template operator()<double, 13, 1, 384>();
         }
     }
 #define SVM_F32_CASE(QQ, TT)                                                    \
@@ -615,7 +617,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 
     // persistent grid: one CTA per SM, fewer for tiny problems
     const int Q = q_for_pitch(ctx->pitch4, ctx->x_f64);
-    int threads = ctx->x_f64 ? 384 : 512;
+    int threads = ctx->x_f64 ? (Q == 13 && !getenv("SVMB200_F64_ONE_ROW") ? 256 : 384) : 512;
     if (Q == 7 && !ctx->x_f64) {
         threads = SMO_DEFAULT_THREADS_Q7;
         if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py
@@ -627,7 +629,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     // ring depth per warp: 4 rows with the 12-warp CTA of the MNIST shape (12 x 4 x 3136 B = 147 KB per SM in flight), 2 elsewhere
     // (with 16 warps two rows per warp already saturate HBM and deeper rings only lengthen the queues the exchange waits behind)
     // (the 8-warp CTA takes four rows per step: a slot is a group of four rows, one in use + one in flight)
-    const int rps = (Q == 7 && !ctx->x_f64 && threads <= 256) ? 4 : 1;      // = smo_rows_per_step<XT, Q, THREADS>()
+    const int rps = (Q == 7 && !ctx->x_f64 && threads <= 256) ? 4 : (Q == 13 && ctx->x_f64 && threads == 256) ? 2 : 1;   // = smo_rows_per_step<XT, Q, THREADS>()
     int kslots = (Q == 7 && !ctx->x_f64) ? (rps == 4 ? (threads == 192 ? 3 : 2) : 4) : 2;
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
     while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps) > (size_t)ctx->max_smem_optin) --kslots;
@@ -710,7 +712,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         double l2_keep_budget = 80.0 * 1024 * 1024;
         if (const char *e = getenv("SVMB200_L2KEEP_MB")) l2_keep_budget = atof(e) * 1024 * 1024;
         int persist = params->l2_persist;
-        if (persist < 0) persist = rps == 4;
+        if (persist < 0) persist = rps > 1;
         if (x_bytes <= 96.0 * 1024 * 1024) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
         else if (persist) a.keep_per_1024 = (int)std::min(1024.0, 1024.0 * l2_keep_budget / x_bytes);
     }

@@ -78,9 +78,13 @@ struct SmoArgs {
 
 // Rows a warp takes per step of the X pass.  1: a row at a time (two sums per butterfly).  4 (fp32 rows, Q = 7, the 8-warp
 // CTA): the ring holds groups of four consecutive rows (one bulk copy, one mbarrier per group); four rows x two pivots =
-// eight sums per halving exchange, eight independent accumulation chains.
+// eight sums per halving exchange, eight independent accumulation chains.  2: the same with FP64 rows (Q = 13), whose
+// rows are twice as long.
 template <typename XT, int Q, int THREADS>
-constexpr int smo_rows_per_step() { return (sizeof(XT) == 4 && Q == 7 && THREADS <= 256) ? 4 : 1; }
+constexpr int smo_rows_per_step()
+{
+    return (sizeof(XT) == 4 && Q == 7 && THREADS <= 256) ? 4 : (sizeof(XT) == 8 && Q == 13 && THREADS == 256) ? 2 : 1;
+}
 
 // ------------------------------------------------------------------------------------------
 template <typename Vec, int Q>
@@ -572,10 +576,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         if (!use_cache) {
             // ---------------- X pass: a warp per row ----------------
             ++x_passes;
-            if constexpr (RPS == 4) {
-              int qoff[Q];                       // byte offset of this lane's 16-byte group in each register group, clamped into the row
-#pragma unroll
-              for (int i = 0; i < Q; ++i) qoff[i] = min(i * 32 + lane, a.pitch4 - 1) * 16;
+            if constexpr (RPS > 1) {
+              constexpr bool NEUTRAL_PAD = sizeof(XT) == 4;   // fp32 rows form dot products: an element times a zero pivot register adds +-0.
+                                                              // FP64 rows form squared differences: elements beyond the row must be skipped
+              const int q_last = min((Q - 1) * 32 + lane, a.pitch4 - 1) * 16;     // byte offset of the lane's last 16-byte group, clamped into the row
+              const bool last_valid = (Q - 1) * 32 + lane < a.pitch4;
               const bool full_groups = (Q - 1) * 32 < a.pitch4;   // every register group reaches into the row
               for (int base = 0; base < m; base += 32) {
                 const int cnt = min(32, m - base);
@@ -584,39 +589,45 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 int yj = 0;
                 long long qj = -1;
                 double nj = 0.0;
-                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; nj = a.sqn[j]; if (a.cacheq) qj = a.cacheq[j]; }
-                for (int t = 0; t < cnt; t += 4) {
-                    const int rows_here = min(4, cnt - t);
+                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; if (sizeof(XT) == 4) nj = a.sqn[j]; if (a.cacheq) qj = a.cacheq[j]; }
+                for (int t = 0; t < cnt; t += RPS) {
+                    const int rows_here = min(RPS, cnt - t);
                     mbar_wait(&my_bars[cslot], cphase);
-                    const unsigned char *grp = my_slots + (size_t)cslot * 4 * row_bytes;
-                    // the lane's partial sums of rows t..t+3 against both pivots: [pivot * 4 + row].  No per-lane bounds test:
-                    // the pivot registers are zero beyond the row and the index is clamped (such an element adds +-0).
-                    double P[8];
+                    const unsigned char *grp = my_slots + (size_t)cslot * RPS * row_bytes;
+                    // the lane's partial sums of rows t..t+RPS-1 against both pivots: [pivot * RPS + row]
+                    double P[2 * RPS];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) P[k] = 0.0;
-                    if (rows_here == 4 && full_groups) {
+                    for (int k = 0; k < 2 * RPS; ++k) P[k] = 0.0;
+                    if (rows_here == RPS && full_groups) {
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) {
-                            // one address per row: the groups 0..Q-2 sit at constant offsets from it, only the last is clamped
+                        for (int r = 0; r < RPS; ++r) {
+                            // one address per row: the groups 0..Q-2 sit at constant offsets from it, no bounds test
                             const unsigned char *rowp = grp + (size_t)r * row_bytes;
                             const Vec *lanep = reinterpret_cast<const Vec *>(rowp) + lane;
 #pragma unroll
-                            for (int i = 0; i < Q; ++i) {
-                                const Vec v = i < Q - 1 ? lanep[i * 32] : *reinterpret_cast<const Vec *>(rowp + qoff[Q - 1]);
+                            for (int i = 0; i < Q - 1; ++i) {
+                                const Vec v = lanep[i * 32];
                                 accum_pair<CH>(v, pv.h[i], P[r]);
-                                accum_pair<CH>(v, pv.l[i], P[4 + r]);
+                                accum_pair<CH>(v, pv.l[i], P[RPS + r]);
+                            }
+                            if (NEUTRAL_PAD || last_valid) {
+                                const Vec v = *reinterpret_cast<const Vec *>(rowp + q_last);
+                                accum_pair<CH>(v, pv.h[Q - 1], P[r]);
+                                accum_pair<CH>(v, pv.l[Q - 1], P[RPS + r]);
                             }
                         }
                     } else {
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) {
+                        for (int r = 0; r < RPS; ++r) {
                             if (r < rows_here) {
+                                const Vec *row = reinterpret_cast<const Vec *>(grp + (size_t)r * row_bytes);
 #pragma unroll
                                 for (int i = 0; i < Q; ++i) {
-                                    if (i * 32 < a.pitch4) {
-                                        const Vec v = *reinterpret_cast<const Vec *>(grp + (size_t)r * row_bytes + qoff[i]);
+                                    const int q = i * 32 + lane;
+                                    if (NEUTRAL_PAD ? i * 32 < a.pitch4 : q < a.pitch4) {
+                                        const Vec v = row[min(q, a.pitch4 - 1)];
                                         accum_pair<CH>(v, pv.h[i], P[r]);
-                                        accum_pair<CH>(v, pv.l[i], P[4 + r]);
+                                        accum_pair<CH>(v, pv.l[i], P[RPS + r]);
                                     }
                                 }
                             }
@@ -627,28 +638,45 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     fence_proxy_async();
                     issue_into(cslot);
                     if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
-                    // halving exchange: offset 16 splits by pivot, 8 and 4 by row, 2 and 1 add.  Each addition pairs the same
-                    // operands as the xor butterfly, so lane l ends with the butterfly's value for pivot l >> 4, row (l >> 2) & 3
-                    double v4[4], v2[2], v1;
-                    {
-                        const bool up = (lane & 16) != 0;
+                    // halving exchange: offset 16 splits by pivot, the next offsets by row (8 and 4 for four rows, 8 for two), the
+                    // rest add.  Each addition pairs the same operands as the xor butterfly, so a lane ends with the butterfly's
+                    // value for pivot lane >> 4 and row (lane >> 2) & 3 (four rows) / (lane >> 3) & 1 (two rows)
+                    double v1;
+                    if constexpr (RPS == 4) {
+                        double v4[4], v2[2];
+                        {
+                            const bool up = (lane & 16) != 0;
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) v4[k] = (up ? P[4 + k] : P[k]) + __shfl_xor_sync(FULL, up ? P[k] : P[4 + k], 16);
-                    }
-                    {
-                        const bool up = (lane & 8) != 0;
+                            for (int k = 0; k < 4; ++k) v4[k] = (up ? P[4 + k] : P[k]) + __shfl_xor_sync(FULL, up ? P[k] : P[4 + k], 16);
+                        }
+                        {
+                            const bool up = (lane & 8) != 0;
 #pragma unroll
-                        for (int k = 0; k < 2; ++k) v2[k] = (up ? v4[2 + k] : v4[k]) + __shfl_xor_sync(FULL, up ? v4[k] : v4[2 + k], 8);
-                    }
-                    {
-                        const bool up = (lane & 4) != 0;
-                        v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 4);
+                            for (int k = 0; k < 2; ++k) v2[k] = (up ? v4[2 + k] : v4[k]) + __shfl_xor_sync(FULL, up ? v4[k] : v4[2 + k], 8);
+                        }
+                        {
+                            const bool up = (lane & 4) != 0;
+                            v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 4);
+                        }
+                    } else {
+                        double v2[2];
+                        {
+                            const bool up = (lane & 16) != 0;
+#pragma unroll
+                            for (int k = 0; k < 2; ++k) v2[k] = (up ? P[2 + k] : P[k]) + __shfl_xor_sync(FULL, up ? P[k] : P[2 + k], 16);
+                        }
+                        {
+                            const bool up = (lane & 8) != 0;
+                            v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 8);
+                        }
+                        v1 = v1 + __shfl_xor_sync(FULL, v1, 4);
                     }
                     v1 = v1 + __shfl_xor_sync(FULL, v1, 2);
                     v1 = v1 + __shfl_xor_sync(FULL, v1, 1);
-                    if ((lane & 3) == 0) {
-                        const int r = (lane >> 2) & 3;
-                        if (r < rows_here) *(reinterpret_cast<double *>(&stage[t + r]) + (lane >> 4)) = v1;
+                    {
+                        const int r = RPS == 4 ? (lane >> 2) & 3 : (lane >> 3) & 1;
+                        const bool writer = RPS == 4 ? (lane & 3) == 0 : (lane & 7) == 0;
+                        if (writer && r < rows_here) *(reinterpret_cast<double *>(&stage[t + r]) + (lane >> 4)) = v1;
                     }
                 }
                 __syncwarp();

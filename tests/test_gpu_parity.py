@@ -255,7 +255,7 @@ def test_model_save_and_load(solver, pkg, dataset, tmp_path):
     assert out["n_sv"] == len(solver.sv_ids())
 
 
-@pytest.mark.parametrize("d", [1, 4, 30, 100, 257, 1024])
+@pytest.mark.parametrize("d", [1, 4, 30, 100, 257, 600, 770, 1024])
 def test_other_feature_counts(solver, O, d):
     rng = np.random.default_rng(d)
     n = 300
@@ -272,6 +272,10 @@ def test_other_feature_counts(solver, O, d):
     assert np.array_equal(out["alpha"], dev["alpha"]) and out["b"] == dev["b"]
     ref = O.smo_train(xs, y, params=p)
     assert np.array_equal(solver.sv_ids(), O.sv_indices(ref["alpha"]))
+    # the decision function at this shape (register groups partly or wholly beyond the row take other code paths)
+    c_dev, s_dev = O.predict(xs[:77], y[:77], xs, y, out["alpha"], out["b"], gamma=gamma, arith=O.ARITH_DEVICE)
+    c_gpu, s_gpu = solver.predict_f64(X[:77], y[:77])
+    assert c_gpu == c_dev and np.array_equal(s_gpu, s_dev)
 
 
 def test_abnormal_stops_are_stats_not_errors(solver, O, dataset, pkg):
