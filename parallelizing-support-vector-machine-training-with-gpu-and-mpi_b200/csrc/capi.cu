@@ -443,16 +443,24 @@ static cudaError_t dispatch(const KernelKey &k, F &&fn)
     case 2: return fn.template operator()<float, QQ, 2, TT>();                   \
     default: return fn.template operator()<float, QQ, 4, TT>();                  \
     }
+    // 256 threads: the SMO kernel's rows-in-groups form; 512 (384 for Q = 7): a row per step, and every other kernel
     switch (k.Q) {
-    case 1: SVM_F32_CASE(1, 512)
-    case 2: SVM_F32_CASE(2, 512)
-    case 4: SVM_F32_CASE(4, 512)
+    case 1:
+        if (k.threads == 256) { SVM_F32_CASE(1, 256) }
+        SVM_F32_CASE(1, 512)
+    case 2:
+        if (k.threads == 256) { SVM_F32_CASE(2, 256) }
+        SVM_F32_CASE(2, 512)
+    case 4:
+        if (k.threads == 256) { SVM_F32_CASE(4, 256) }
+        SVM_F32_CASE(4, 512)
     case 7:
-        if (k.threads == 192) { SVM_F32_CASE(7, 192) }
         if (k.threads == 256) { SVM_F32_CASE(7, 256) }
         if (k.threads == 384) { SVM_F32_CASE(7, 384) }
         SVM_F32_CASE(7, 512)
-    default: SVM_F32_CASE(8, 512)
+    default:
+        if (k.threads == 256) { SVM_F32_CASE(8, 256) }
+        SVM_F32_CASE(8, 512)
     }
 #undef SVM_F32_CASE
 }
@@ -565,7 +573,7 @@ static int ensure_norms(svmb200_ctx *ctx, int CH)
 
 // 8 warps x four rows per step (242 registers, no spills) + L2-resident share of X: 25.9 us/iteration at 60k; 12 warps x one row per
 // step (165 registers): 33.4; 16 warps (128 registers, spills): 35.4
-static const int SMO_DEFAULT_THREADS_Q7 = 256;
+static const int SMO_DEFAULT_THREADS = 256;
 static const int DEFAULT_CHUNK = 4;   // fp32 storage of X dominates the error of K for every chunk (DESIGN.md "Numerics")
 
 static int resolve_chunk(int c)
@@ -617,20 +625,17 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 
     // persistent grid: one CTA per SM, fewer for tiny problems
     const int Q = q_for_pitch(ctx->pitch4, ctx->x_f64);
-    int threads = ctx->x_f64 ? (Q == 13 && !getenv("SVMB200_F64_ONE_ROW") ? 256 : 384) : 512;
-    if (Q == 7 && !ctx->x_f64) {
-        threads = SMO_DEFAULT_THREADS_Q7;
-        if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py
+    // fp32 rows: 8 warps taking rows in groups (SMO_DEFAULT_THREADS); FP64 rows: the same for the longest rows (Q = 13), else 12 warps, a row per step
+    int threads = ctx->x_f64 ? (Q == 13 && !getenv("SVMB200_F64_ONE_ROW") ? 256 : 384) : SMO_DEFAULT_THREADS;
+    if (!ctx->x_f64)
+        if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py: 512 (384 at Q = 7) = a row per step
             const int t = atoi(e);
-            if (t == 192 || t == 256 || t == 384 || t == 512) threads = t;
+            if (t == 256 || t == 512 || (t == 384 && Q == 7)) threads = t;
         }
-    }
     const int warps = threads / 32;
-    // ring depth per warp: 4 rows with the 12-warp CTA of the MNIST shape (12 x 4 x 3136 B = 147 KB per SM in flight), 2 elsewhere
-    // (with 16 warps two rows per warp already saturate HBM and deeper rings only lengthen the queues the exchange waits behind)
-    // (the 8-warp CTA takes four rows per step: a slot is a group of four rows, one in use + one in flight)
-    const int rps = (Q == 7 && !ctx->x_f64 && threads <= 256) ? 4 : (Q == 13 && ctx->x_f64 && threads == 256) ? 2 : 1;   // = smo_rows_per_step<XT, Q, THREADS>()
-    int kslots = (Q == 7 && !ctx->x_f64) ? (rps == 4 ? (threads == 192 ? 3 : 2) : 4) : 2;
+    const int rps = !ctx->x_f64 ? (threads <= 256 ? (Q == 8 ? 2 : 4) : 1) : (Q == 13 && threads == 256) ? 2 : 1;   // = smo_rows_per_step<XT, Q, THREADS>()
+    // ring depth: as many groups as fit, at most 4 (two at the MNIST shape: one in use, one in flight); a row per step: 4 rows at Q = 7, else 2
+    int kslots = rps > 1 ? 4 : (Q == 7 && !ctx->x_f64) ? 4 : 2;
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
     while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps) > (size_t)ctx->max_smem_optin) --kslots;
     const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps);

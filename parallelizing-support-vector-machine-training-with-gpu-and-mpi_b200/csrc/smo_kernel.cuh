@@ -23,6 +23,7 @@
 // All mutable state (f, alpha, cache slots, cache bookkeeping) of row j is touched only by the CTA
 // that owns row j, so the record exchange is the only cross-CTA communication.
 #pragma once
+#include <type_traits>
 #include "device_math.cuh"
 
 namespace svm {
@@ -76,14 +77,14 @@ struct SmoArgs {
     int timing_cap;
 };
 
-// Rows a warp takes per step of the X pass.  1: a row at a time (two sums per butterfly).  4 (fp32 rows, Q = 7, the 8-warp
-// CTA): the ring holds groups of four consecutive rows (one bulk copy, one mbarrier per group); four rows x two pivots =
+// Rows a warp takes per step of the X pass.  1: a row at a time (two sums per butterfly).  4 (fp32 rows, the 8-warp
+// CTA; 2 for the longest rows, Q = 8): the ring holds groups of four consecutive rows (one bulk copy, one mbarrier per group); four rows x two pivots =
 // eight sums per halving exchange, eight independent accumulation chains.  2: the same with FP64 rows (Q = 13), whose
 // rows are twice as long.
 template <typename XT, int Q, int THREADS>
 constexpr int smo_rows_per_step()
 {
-    return (sizeof(XT) == 4 && Q == 7 && THREADS <= 256) ? 4 : (sizeof(XT) == 8 && Q == 13 && THREADS == 256) ? 2 : 1;
+    return (sizeof(XT) == 4 && THREADS <= 256) ? (Q == 8 ? 2 : 4) : (sizeof(XT) == 8 && Q == 13 && THREADS == 256) ? 2 : 1;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -110,6 +111,33 @@ __device__ __forceinline__ void row_dot2(const Vec *__restrict__ row, const Pivo
     warp_sum_butterfly2(ah, al, lane);
     dh = ah;
     dl = al;
+}
+
+// One full group of RPS rows against both pivots, NG = the number of 32-lane register groups the row really has
+// (the kernel is instantiated for a class of row lengths, Q >= NG): groups 0..NG-2 are whole and sit at constant
+// offsets from one address per row; the last is read at a clamped offset (fp32: the pivot registers are zero beyond the
+// row, so such an element adds +-0) or skipped per lane (FP64 rows accumulate squared differences).
+template <typename Vec, int Q, int CH, int RPS, int NG>
+__device__ __forceinline__ void group_dot2(const unsigned char *grp, int row_bytes, int lane, int q_last, bool last_valid,
+                                           const Pivots<Vec, Q> &pv, double (&P)[2 * RPS])
+{
+    constexpr bool NEUTRAL_PAD = sizeof(Vec) == sizeof(float4) && std::is_same<Vec, float4>::value;
+#pragma unroll
+    for (int r = 0; r < RPS; ++r) {
+        const unsigned char *rowp = grp + (size_t)r * row_bytes;
+        const Vec *lanep = reinterpret_cast<const Vec *>(rowp) + lane;
+#pragma unroll
+        for (int i = 0; i < NG - 1; ++i) {
+            const Vec v = lanep[i * 32];
+            accum_pair<CH>(v, pv.h[i], P[r]);
+            accum_pair<CH>(v, pv.l[i], P[RPS + r]);
+        }
+        if (NEUTRAL_PAD || last_valid) {
+            const Vec v = *reinterpret_cast<const Vec *>(rowp + q_last);
+            accum_pair<CH>(v, pv.h[NG - 1], P[r]);
+            accum_pair<CH>(v, pv.l[NG - 1], P[RPS + r]);
+        }
+    }
 }
 
 // membership tests of calc_i_high / calc_i_low (code/main3.cpp:115,134)
@@ -579,9 +607,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             if constexpr (RPS > 1) {
               constexpr bool NEUTRAL_PAD = sizeof(XT) == 4;   // fp32 rows form dot products: an element times a zero pivot register adds +-0.
                                                               // FP64 rows form squared differences: elements beyond the row must be skipped
-              const int q_last = min((Q - 1) * 32 + lane, a.pitch4 - 1) * 16;     // byte offset of the lane's last 16-byte group, clamped into the row
-              const bool last_valid = (Q - 1) * 32 + lane < a.pitch4;
-              const bool full_groups = (Q - 1) * 32 < a.pitch4;   // every register group reaches into the row
+              const int ng = (a.pitch4 + 31) >> 5;                                 // register groups the row really has (<= Q)
+              const int q_last = min((ng - 1) * 32 + lane, a.pitch4 - 1) * 16;     // byte offset of the lane's last 16-byte group, clamped into the row
+              const bool last_valid = (ng - 1) * 32 + lane < a.pitch4;
               for (int base = 0; base < m; base += 32) {
                 const int cnt = min(32, m - base);
                 const long long j = w0 + base + lane;
@@ -598,22 +626,24 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     double P[2 * RPS];
 #pragma unroll
                     for (int k = 0; k < 2 * RPS; ++k) P[k] = 0.0;
-                    if (rows_here == RPS && full_groups) {
+                    if (rows_here == RPS) {
+                        // Q is the largest group count of its class: 1, 2, 3-4, 5-7, 8 (fp32) / 13 (FP64); ng is warp-uniform
+                        if (ng == Q) group_dot2<Vec, Q, CH, RPS, Q>(grp, row_bytes, lane, q_last, last_valid, pv, P);
+                        else if (Q >= 2 && ng == Q - 1) group_dot2<Vec, Q, CH, RPS, (Q >= 2 ? Q - 1 : 1)>(grp, row_bytes, lane, q_last, last_valid, pv, P);
+                        else if (Q >= 3 && ng == Q - 2) group_dot2<Vec, Q, CH, RPS, (Q >= 3 ? Q - 2 : 1)>(grp, row_bytes, lane, q_last, last_valid, pv, P);
+                        else {
 #pragma unroll
-                        for (int r = 0; r < RPS; ++r) {
-                            // one address per row: the groups 0..Q-2 sit at constant offsets from it, no bounds test
-                            const unsigned char *rowp = grp + (size_t)r * row_bytes;
-                            const Vec *lanep = reinterpret_cast<const Vec *>(rowp) + lane;
+                            for (int r = 0; r < RPS; ++r) {
+                                const Vec *row = reinterpret_cast<const Vec *>(grp + (size_t)r * row_bytes);
 #pragma unroll
-                            for (int i = 0; i < Q - 1; ++i) {
-                                const Vec v = lanep[i * 32];
-                                accum_pair<CH>(v, pv.h[i], P[r]);
-                                accum_pair<CH>(v, pv.l[i], P[RPS + r]);
-                            }
-                            if (NEUTRAL_PAD || last_valid) {
-                                const Vec v = *reinterpret_cast<const Vec *>(rowp + q_last);
-                                accum_pair<CH>(v, pv.h[Q - 1], P[r]);
-                                accum_pair<CH>(v, pv.l[Q - 1], P[RPS + r]);
+                                for (int i = 0; i < Q; ++i) {
+                                    const int q = i * 32 + lane;
+                                    if (NEUTRAL_PAD ? i * 32 < a.pitch4 : q < a.pitch4) {
+                                        const Vec v = row[min(q, a.pitch4 - 1)];
+                                        accum_pair<CH>(v, pv.h[i], P[r]);
+                                        accum_pair<CH>(v, pv.l[i], P[RPS + r]);
+                                    }
+                                }
                             }
                         }
                     } else {
