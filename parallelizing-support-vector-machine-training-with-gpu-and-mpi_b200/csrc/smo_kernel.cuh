@@ -507,14 +507,19 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
 
         // cached iteration: this thread's first row of the pass is requested now, so that its loads and the K12 load
         // below travel together instead of one L2 round trip after the other
-        const long long pj = r0 + threadIdx.x;
-        double p_f = 0.0, p_a = 0.0, p_kh = 0.0, p_kl = 0.0;
-        int p_y = 0;
-        long long p_q = -1;
+        const long long pj = r0 + threadIdx.x, pj2 = pj + THREADS;
+        double p_f = 0.0, p_a = 0.0, p_kh = 0.0, p_kl = 0.0, p2_f = 0.0, p2_a = 0.0, p2_kh = 0.0, p2_kl = 0.0;
+        int p_y = 0, p2_y = 0;
+        long long p_q = -1, p2_q = -1;
         if (use_cache && pj < r1) {
             p_f = a.f[pj]; p_a = a.alpha[pj]; p_y = a.y[pj]; p_q = a.cacheq[pj];
             p_kh = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + pj];
             p_kl = a.cacheK[(size_t)(q_l % a.cache_cap) * a.n + pj];
+            if (pj2 < r1) {              // a CTA owns more rows than it has threads (405 against 256 at 60k): the second row's loads travel now too
+                p2_f = a.f[pj2]; p2_a = a.alpha[pj2]; p2_y = a.y[pj2]; p2_q = a.cacheq[pj2];
+                p2_kh = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + pj2];
+                p2_kl = a.cacheK[(size_t)(q_l % a.cache_cap) * a.n + pj2];
+            }
         }
 
         // K12 = K(i_high, i_low)  (main3.cpp:241)
@@ -766,11 +771,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             const double *kh_row = a.cacheK + (size_t)slot_h * a.n;
             const double *kl_row = a.cacheK + (size_t)slot_l * a.n;
             for (long long j = pj; j < r1; j += THREADS) {
-                const bool first = j == pj;
-                double fj = first ? p_f : a.f[j], aj = first ? p_a : a.alpha[j];
-                const int yj = first ? p_y : a.y[j];
-                const long long qj = first ? p_q : a.cacheq[j];
-                const double khj = first ? p_kh : kh_row[j], klj = first ? p_kl : kl_row[j];
+                const bool first = j == pj, second = j == pj2;
+                double fj = first ? p_f : second ? p2_f : a.f[j], aj = first ? p_a : second ? p2_a : a.alpha[j];
+                const int yj = first ? p_y : second ? p2_y : a.y[j];
+                const long long qj = first ? p_q : second ? p2_q : a.cacheq[j];
+                const double khj = first ? p_kh : second ? p2_kh : kh_row[j], klj = first ? p_kl : second ? p2_kl : kl_row[j];
                 fj = fj + (c_h * khj + c_l * klj);
                 a.f[j] = fj;
                 if (j == i_high) { aj = na_h; a.alpha[j] = aj; }
