@@ -9,16 +9,18 @@
 //        record exchange, and redoes the scalar update redundantly (main3.cpp:235-270): K12, eta,
 //        U/V, clipped alpha_low', alpha_high', the two f coefficients -- identical bits everywhere,
 //        so no broadcast is needed;
-//     2. X pass (a warp per row): the row arrives in shared memory by bulk copy (TMA, one 3136-byte
-//        copy per row into a warp-private ring that keeps running across iterations), both squared
-//        distances to the pivot rows held in registers are formed in one read of the row
-//        (main3.cpp:221-222,230-231), f[j] is updated in the same pass (:271-275), and the row
-//        joins the warp's running (value, lowest-index) argmin over I_high / argmax over I_low
-//        (:107-142) with the pair's new alphas already applied (:278-279);
+//     2. X pass (a warp per group of four consecutive rows; two for the longest rows, one in the one-row variants): the
+//        group arrives in shared memory by ONE bulk copy (TMA) into a warp-private ring that keeps running across
+//        iterations, both dot products (FP64 rows: squared distances) with the pivot rows held in registers are formed
+//        in one read of each row (main3.cpp:221-222,230-231), the 2 x 4 warp sums by one halving exchange, f[j] is
+//        updated in the same pass (:271-275), and the row joins the warp's running (value, lowest-index) argmin over
+//        I_high / argmax over I_low (:107-142) with the pair's new alphas already applied (:278-279).  A share of X is
+//        loaded with an evict-last policy and stays in L2 from one pass to the next;
 //        -- or, when both kernel rows are in the HBM row cache, a thread-per-row pass over the two
 //        cached rows instead of X;
-//     3. reduces its candidates, publishes one 64-byte record with a release store, and acquires
-//        all other CTAs' records (an all-gather through L2: the only grid-wide synchronisation).
+//     3. reduces its candidates, publishes one 128-byte self-validating record, adds 1 to an arrival counter, and
+//        reads all other CTAs' records once the count is complete (an all-gather through L2: the only grid-wide
+//        synchronisation).
 //
 // All mutable state (f, alpha, cache slots, cache bookkeeping) of row j is touched only by the CTA
 // that owns row j, so the record exchange is the only cross-CTA communication.
@@ -607,7 +609,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         SVM_STAMP(1);
         SVM_GSTAMP(1);
         if (!use_cache) {
-            // ---------------- X pass: a warp per row ----------------
+            // ---------------- X pass: a warp per group of RPS rows (or per row, below) ----------------
             ++x_passes;
             if constexpr (RPS > 1) {
               constexpr bool NEUTRAL_PAD = sizeof(XT) == 4;   // fp32 rows form dot products: an element times a zero pivot register adds +-0.
