@@ -289,6 +289,9 @@ def run_ours(args):
     if os.path.exists(prof):
         try:
             roofline["traffic"] = json.load(open(prof)).get("dram_bytes_per_iteration")
+            # the DRAM side of the same launch: measured bytes per iteration (ncu) over this run's time per iteration
+            roofline["dram_achieved"] = roofline["traffic"] / (ms_per_step * 1e-3) / 1e9
+            roofline["dram_frac"] = roofline["dram_achieved"] / peak
         except Exception:
             pass
 

@@ -413,6 +413,11 @@ def test_full_size_60k_against_reference_fixture_and_invariants(solver, dataset)
     for i in (0, 12345, 59999, int(sv[0]), int(sv[-1])):
         k = solver.kernel_row(i)
         assert abs(float(np.dot(alpha[sv] * y[sv], k[sv])) - y[i] - f[i]) < 1e-8
+    # memory-side choices change no bit: the L2-resident share of X off / on, the row cache off / on
+    # (only at this size do the rows exceed L2, so only here is the residency policy in force)
+    runs = [solver.smo_train(max_iter=1500, cache_rows=c, l2_persist=p, trace_cap=1500) for c, p in ((0, 0), (0, 1), (-1, 1))]
+    for r in runs[1:]:
+        assert np.array_equal(r["alpha"], runs[0]["alpha"]) and r["b"] == runs[0]["b"] and r["num_iter"] == runs[0]["num_iter"]
 
 
 def test_full_size_60k_exact_path_is_the_reference_run(exact_solver, dataset):
