@@ -90,3 +90,18 @@ def test_cascade_on_gpu_matches_reference(mode, pkg, tmp_path, tmp_path_factory)
     if os.path.exists(REF[mode]):
         ref = _reference(mode, 2, pkg, tmp_path_factory)
         assert len(ours["sv_ids"]) == ref["sv_count"] and ours["correct"] == ref["correct"]
+
+
+def test_cascade_program_reads_the_reference_csv(tmp_path):
+    """cascade_main.read_reference_csv follows code/main3.cpp:13-54: header line dropped, last column = digit."""
+    import importlib.util
+    import numpy as np
+    import __graft_entry__ as entry
+    pkg = entry.load_package()
+    spec = importlib.util.spec_from_file_location("cascade_main", os.path.join(os.path.dirname(pkg.__file__), "cascade_main.py"))
+    cm = importlib.util.module_from_spec(spec); spec.loader.exec_module(cm)
+    X, dg = pkg.datagen.make_dataset(25)
+    path = str(tmp_path / "mnist3_train_data.csv")
+    pkg.datagen.write_csv(path, X, dg)
+    X2, dg2 = cm.read_reference_csv(path)
+    assert X2.shape == (25, 784) and np.array_equal(X2, X.astype(np.float64)) and np.array_equal(dg2, dg)

@@ -45,3 +45,39 @@ def test_row_sharding_host_logic_over_gloo(world, n, tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, OMP_NUM_THREADS="1"))
     assert r.returncode == 0, r.stderr[-3000:]
     assert json.load(open(out)) == [True] * world
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["star", "tree"])
+def test_cascade_program_on_two_gpus(mode):
+    """The program that stands where mpi_svm_main2/3 stand: two ranks, 4 000 synthetic rows; its report must name the
+    SV count and accuracy of the undivided problem solved on one GPU."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    import re
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as entry
+    pkg = entry.load_package()
+    n = 4000
+    X, dg = pkg.datagen.make_dataset(n); y = pkg.datagen.binary_labels(dg)
+    Xt, dgt = pkg.datagen.make_dataset(10000, split=1); yt = pkg.datagen.binary_labels(dgt)
+    s = pkg.Solver(0)
+    try:
+        s.set_train_u8(X, y)
+        full = s.smo_train(cache_rows=-1)
+        correct, _ = s.predict_u8(Xt, yt, ge_zero=True)
+    finally:
+        s.close()
+    prog = os.path.join(ROOT, "parallelizing-support-vector-machine-training-with-gpu-and-mpi_b200", "cascade_main.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29411", prog, "--mode", mode, "--synthetic", str(n)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    out = r.stdout
+    print(out[-800:])
+    assert re.search(r"\[rank 0\] Converged at round \d+, SV count = (\d+)", out)
+    assert int(re.search(r"Final global SV count = (\d+)", out).group(1)) == full["n_sv"]
+    assert int(re.search(r"Test accuracy \(final model\) = [0-9.]+ \((\d+)/10000\)", out).group(1)) == correct
+    b = float(re.search(r"Final b = ([-0-9.e]+)", out).group(1))
+    assert abs(b - full["b"]) <= 1e-4 * max(1.0, abs(full["b"]))
