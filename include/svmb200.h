@@ -115,6 +115,21 @@ int svmb200_set_labels(svmb200_ctx *ctx, const int32_t *y);
  * (DESIGN.md "Numerics").  Exact storage takes d <= 832. */
 int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable);
 
+/* The same choice with a third option.  SVMB200_STORAGE_U8 (svmb200_set_train_u8 only; other uploads then fail with
+ * SVMB200_ESTATE) keeps X as the bytes it arrived as -- a quarter of the fp32 bytes, so 60 000 x 784 rows stay in L2 from one
+ * iteration to the next.  For integer-valued input min and range are integers and the reference's scaled squared difference
+ * (main3.cpp:74-89, :97-100) is (u_k - p_k)^2 / range_k^2: the features that share the most frequent range are summed as exact
+ * integers (four products per IDP4A), the rest in FP64 with their weights (DESIGN.md "Numerics").  K agrees with the reference's
+ * to ~1e-16 and the solver walks the reference's own (i_high, i_low) sequence, like FP64 storage, at a fraction of the bytes.
+ * The decision function (svmb200_predict_*, warm start) then works on scaled FP64 rows.  d <= 832. */
+#define SVMB200_STORAGE_F32 0
+#define SVMB200_STORAGE_F64 1
+#define SVMB200_STORAGE_U8  2
+int svmb200_set_storage(svmb200_ctx *ctx, int32_t storage);
+/* layout of the packed uint8 rows of the current training set (introspection): the range shared by the main class
+ * (0 = none), the features in it, the features in the weighted tail, bytes per packed row */
+int svmb200_get_u8_layout(svmb200_ctx *ctx, int32_t *main_range, int32_t *main_features, int32_t *tail_features, int32_t *row_bytes);
+
 /* X already scaled by the caller -- exactly what the reference's SMO_train receives
  * (main3.cpp:347).  No statistics are computed; svmb200_predict_scaled_f64 is the matching call. */
 int svmb200_set_train_scaled_f64(svmb200_ctx *ctx, const double *Xs, const int32_t *y, int64_t n, int32_t d);
@@ -192,6 +207,12 @@ int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_
  * (main3.cpp:107-142): lowest index wins ties; n when the set is empty */
 int svmb200_select_pair(svmb200_ctx *ctx, const double *alpha, const double *f, const int32_t *y,
                         int64_t n, double C, double eps, int64_t *i_high, int64_t *i_low);
+/* the scalar part of one iteration exactly as the solver runs it: calculate_U_V (main3.cpp:145-159) and the pair
+ * update (:235-270) for a pair with labels y_high / y_low, alphas, b_high = f[i_high], b_low = f[i_low] and
+ * K12 = K(i_high, i_low).  out7 = {U, V, eta, alpha_high', alpha_low', delta_alpha_high * y_high, delta_alpha_low * y_low};
+ * *stop = 0, SVMB200_STOP_INFEASIBLE (:246) or SVMB200_STOP_ETA (:253), in which case the alphas are returned unchanged */
+int svmb200_pair_update(svmb200_ctx *ctx, int32_t y_high, int32_t y_low, double alpha_high, double alpha_low,
+                        double b_high, double b_low, double K12, double C, double eps, double *out7, int32_t *stop);
 /* the scaled fp32 training matrix as stored in HBM (n x d, padding stripped) */
 int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs);
 
@@ -209,6 +230,8 @@ int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs);
  *     without waiting: the results are ready when the stream reaches that point;
  *   - the first call on each device looks up the table's address (one-time set-up): make that first
  *     call before starting any stream capture on that device;
+ *   - that one-time set-up is not locked: two host threads making the first call on the same device at the same
+ *     time both look the address up and both store the same value, which is harmless; later calls only read it;
  *   - all calls on one device share the table, so two calls whose kernels may overlap on the GPU
  *     (different streams, no ordering between them) race; calls on one stream are safe.  The table
  *     keeps the previous call's values, which is harmless: each call writes every entry it reads.

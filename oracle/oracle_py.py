@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ARITH_F64, ARITH_DEVICE, ARITH_DEVICE_F64 = 0, 1, 2
+ARITH_F64, ARITH_DEVICE, ARITH_DEVICE_F64, ARITH_DEVICE_U8 = 0, 1, 2, 3
 DEFAULT_CHUNK = 4   # the library's default svmb200_params.accum_chunk
 STOP_NAMES = {0: "converged", 1: "not_found", 2: "infeasible_uv", 3: "nonpositive_eta", 4: "max_iter"}
 
@@ -84,6 +84,12 @@ def lib():
         L.oracle_device_kernel_f64.argtypes = [_f64(), _f64(), C.c_size_t, C.c_double]
         L.oracle_device_kernel.restype = C.c_double
         L.oracle_device_kernel.argtypes = [_f32(), _f32(), C.c_size_t, C.c_double]
+        L.oracle_u8_bind.argtypes = [_P(dtype=np.uint8, flags="C_CONTIGUOUS"), C.c_size_t, C.c_size_t]
+        L.oracle_u8_layout.argtypes = [C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.oracle_u8_sqdist.restype = C.c_double
+        L.oracle_u8_sqdist.argtypes = [C.c_size_t, C.c_size_t]
+        L.oracle_u8_kernel.restype = C.c_double
+        L.oracle_u8_kernel.argtypes = [C.c_size_t, C.c_size_t, C.c_double]
         _lib = L
     return _lib
 
@@ -121,6 +127,20 @@ def ref():
 def set_device_chunk(ch: int) -> None:
     """Select which svmb200_params.accum_chunk the ORACLE_ARITH_DEVICE arithmetic restates."""
     lib().oracle_set_device_chunk(ch)
+
+
+def u8_bind(rows_u8: np.ndarray):
+    """Bind the raw uint8 training rows for ARITH_DEVICE_U8 (then smo_train(scale(rows)[0], y, arith=ARITH_DEVICE_U8)).
+    Returns (R, M, T): range of the main class, features in it, features in the tail."""
+    rows = np.ascontiguousarray(rows_u8, dtype=np.uint8)
+    lib().oracle_u8_bind(rows, rows.shape[0], rows.shape[1])
+    R, M, T = C.c_int(), C.c_int64(), C.c_int64()
+    lib().oracle_u8_layout(C.byref(R), C.byref(M), C.byref(T))
+    return R.value, M.value, T.value
+
+
+def u8_kernel(row: int, piv: int, gamma: float = 0.00125) -> float:
+    return lib().oracle_u8_kernel(row, piv, gamma)
 
 
 def default_params(**kw) -> Params:

@@ -230,6 +230,133 @@ double oracle_device_kernel_f64(const double *a, const double *b, size_t d, doub
     return oracle_device_exp(-gamma * lane[0]);
 }
 
+
+/* ------------------------------------------------------------------------------------------
+ * The CUDA path for uint8 input kept as uint8 in memory (svmb200 storage "u8", ORACLE_ARITH_DEVICE_U8).
+ * The reference scales every feature to (u - min_k) / range_k in FP64 (code/main3.cpp:74-89) and sums
+ * squared differences (:97-100).  For integer-valued input min_k and range_k are integers and
+ * (a_k - b_k)^2 = (u_k - p_k)^2 / range_k^2, so the device keeps the raw bytes and forms
+ *     d2 = S_main * w_R + tail
+ *   S_main = sum over the features whose range is the most frequent one, R, of (u_k - p_k)^2 : exact integer
+ *   tail   = (N(u) + N(p)) - 2 D(u, p) over the other non-constant features, clamped at 0, with
+ *            D(u, p) = sum_k u_k * (w_k p_k), N(u) = D(u, u), w_k = (1/range_k)^2, in FP64: lane l = g mod 32 owns
+ *            the 4-byte words g of the tail, adds its elements in order with fma, and the 32 lane sums are
+ *            combined by the xor-butterfly 16,8,4,2,1.  D's first argument is the streamed row, the second
+ *            the pivot row.
+ * Constant features (range 0) contribute (u_k - p_k) = 0 and are left out.  K = exp(-gamma d2) (oracle_device_exp).
+ * ------------------------------------------------------------------------------------------ */
+static struct {
+    size_t n, d;
+    int R;                 /* range of the main class (0 = no main class) */
+    size_t M, T;           /* features in the main class / in the tail */
+    int *main_idx, *tail_idx;
+    double wR, *wt;        /* weight of the main class, weights of the tail features */
+    uint8_t *mainb, *tailb;   /* [n][M], [n][T] */
+    int32_t *nmain;        /* [n] integer squared norms over the main class */
+    double *ntail;         /* [n] N(u) over the tail */
+} g_u8;
+
+static double u8_tail_dot(const uint8_t *row, const uint8_t *piv)
+{
+    double lane[32];
+    for (int l = 0; l < 32; ++l) lane[l] = 0.0;
+    for (size_t k = 0; k < g_u8.T; ++k) {
+        size_t g = k / 4;            /* 4-byte word of the tail */
+        double pw = g_u8.wt[k] * (double)piv[k];
+        lane[g & 31] = fma((double)row[k], pw, lane[g & 31]);
+    }
+    for (int off = 16; off >= 1; off >>= 1) {
+        double t[32];
+        for (int l = 0; l < 32; ++l) t[l] = lane[l] + lane[l ^ off];
+        for (int l = 0; l < 32; ++l) lane[l] = t[l];
+    }
+    return lane[0];
+}
+
+void oracle_u8_unbind(void)
+{
+    free(g_u8.main_idx); free(g_u8.tail_idx); free(g_u8.wt); free(g_u8.mainb); free(g_u8.tailb);
+    free(g_u8.nmain); free(g_u8.ntail);
+    memset(&g_u8, 0, sizeof g_u8);
+}
+
+void oracle_u8_bind(const uint8_t *rows, size_t n, size_t d)
+{
+    oracle_u8_unbind();
+    int *range = (int *)calloc(d ? d : 1, sizeof(int));
+    int count[256];
+    memset(count, 0, sizeof count);
+    for (size_t k = 0; k < d; ++k) {
+        int lo = 255, hi = 0;
+        for (size_t i = 0; i < n; ++i) {
+            int v = rows[i * d + k];
+            lo = v < lo ? v : lo;
+            hi = v > hi ? v : hi;
+        }
+        range[k] = n ? hi - lo : 0;
+        count[range[k]]++;
+    }
+    int R = 0;                                  /* most frequent non-zero range; the larger value wins a tie */
+    for (int r = 1; r < 256; ++r)
+        if (count[r] > 0 && (R == 0 || count[r] >= count[R])) R = r;
+    if (R && count[R] < 32) R = 0;              /* too few to be worth an integer section */
+    g_u8.n = n; g_u8.d = d; g_u8.R = R;
+    g_u8.main_idx = (int *)malloc(sizeof(int) * (d ? d : 1));
+    g_u8.tail_idx = (int *)malloc(sizeof(int) * (d ? d : 1));
+    g_u8.wt = (double *)malloc(sizeof(double) * (d ? d : 1));
+    for (size_t k = 0; k < d; ++k) {
+        if (range[k] == 0) continue;
+        if (range[k] == R) g_u8.main_idx[g_u8.M++] = (int)k;
+        else {
+            double s = 1.0 / (double)range[k];
+            g_u8.wt[g_u8.T] = s * s;
+            g_u8.tail_idx[g_u8.T++] = (int)k;
+        }
+    }
+    { double s = R ? 1.0 / (double)R : 0.0; g_u8.wR = s * s; }
+    g_u8.mainb = (uint8_t *)malloc(n * g_u8.M + 1);
+    g_u8.tailb = (uint8_t *)malloc(n * g_u8.T + 1);
+    g_u8.nmain = (int32_t *)malloc(sizeof(int32_t) * (n ? n : 1));
+    g_u8.ntail = (double *)malloc(sizeof(double) * (n ? n : 1));
+    for (size_t i = 0; i < n; ++i) {
+        int32_t nm = 0;
+        for (size_t k = 0; k < g_u8.M; ++k) {
+            uint8_t v = rows[i * d + g_u8.main_idx[k]];
+            g_u8.mainb[i * g_u8.M + k] = v;
+            nm += (int32_t)v * v;
+        }
+        for (size_t k = 0; k < g_u8.T; ++k) g_u8.tailb[i * g_u8.T + k] = rows[i * d + g_u8.tail_idx[k]];
+        g_u8.nmain[i] = nm;
+        g_u8.ntail[i] = u8_tail_dot(g_u8.tailb + i * g_u8.T, g_u8.tailb + i * g_u8.T);
+    }
+    free(range);
+}
+
+void oracle_u8_layout(int *R, int64_t *M, int64_t *T)
+{
+    if (R) *R = g_u8.R;
+    if (M) *M = (int64_t)g_u8.M;
+    if (T) *T = (int64_t)g_u8.T;
+}
+
+/* squared distance of the scaled rows: streamed row `row`, pivot row `piv` (indices into the bound rows) */
+double oracle_u8_sqdist(size_t row, size_t piv)
+{
+    int32_t dotm = 0;
+    const uint8_t *a = g_u8.mainb + row * g_u8.M, *b = g_u8.mainb + piv * g_u8.M;
+    for (size_t k = 0; k < g_u8.M; ++k) dotm += (int32_t)a[k] * b[k];
+    int32_t S = g_u8.nmain[row] + g_u8.nmain[piv] - 2 * dotm;
+    double dt = u8_tail_dot(g_u8.tailb + row * g_u8.T, g_u8.tailb + piv * g_u8.T);
+    double tail = (g_u8.ntail[row] + g_u8.ntail[piv]) - 2.0 * dt;
+    if (tail < 0.0) tail = 0.0;
+    return fma((double)S, g_u8.wR, tail);
+}
+
+double oracle_u8_kernel(size_t row, size_t piv, double gamma)
+{
+    return oracle_device_exp(-gamma * oracle_u8_sqdist(row, piv));
+}
+
 static double device_kernel_n(const float *a, const float *b, double na, double nb, size_t d, double gamma)
 {
     return oracle_device_exp(-gamma * oracle_device_sqdist_n(na, nb, oracle_device_dot(a, b, d)));
@@ -245,6 +372,9 @@ static void kernel_row(const double *x, const float *x32, const double *sqn, siz
     } else if (arith == ORACLE_ARITH_DEVICE_F64) {
         for (size_t j = 0; j < n; ++j)
             row[j] = oracle_device_kernel_f64(x + i * d, x + j * d, d, gamma);
+    } else if (arith == ORACLE_ARITH_DEVICE_U8) {
+        for (size_t j = 0; j < n; ++j)
+            row[j] = oracle_u8_kernel(j, i, gamma);
     } else {
         for (size_t j = 0; j < n; ++j)
             row[j] = device_kernel_n(x32 + i * d, x32 + j * d, sqn[i], sqn[j], d, gamma);
@@ -282,7 +412,7 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
             for (size_t j = 0; j < n; ++j) {
                 if (alpha[j] == 0.0) continue;
                 double kij = (arith == ORACLE_ARITH_F64)          ? oracle_kernel(x + j * d, x + i * d, d, gamma)
-                             : (arith == ORACLE_ARITH_DEVICE_F64) ? oracle_device_kernel_f64(x + j * d, x + i * d, d, gamma)
+                             : (arith == ORACLE_ARITH_DEVICE_F64 || arith == ORACLE_ARITH_DEVICE_U8) ? oracle_device_kernel_f64(x + j * d, x + i * d, d, gamma)
                                                                   : device_kernel_n(x32 + j * d, x32 + i * d, sqn[j], sqn[i], d, gamma);
                 sum += alpha[j] * y[j] * kij;
             }
@@ -395,7 +525,7 @@ int oracle_predict(const double *x_test, const int *y_test, size_t m,
         for (size_t k = 0; k < n_sv; ++k) {
             size_t j = (size_t)sv_idx[k];
             double kv = (arith == ORACLE_ARITH_F64)          ? oracle_kernel(x_test + i * d, x_train + j * d, d, gamma)
-                        : (arith == ORACLE_ARITH_DEVICE_F64) ? oracle_device_kernel_f64(x_test + i * d, x_train + j * d, d, gamma)
+                        : (arith == ORACLE_ARITH_DEVICE_F64 || arith == ORACLE_ARITH_DEVICE_U8) ? oracle_device_kernel_f64(x_test + i * d, x_train + j * d, d, gamma)
                                                              : oracle_device_kernel(t32 + i * d, s32 + k * d, d, gamma);
             curr += alpha[j] * y_train[j] * kv;
         }

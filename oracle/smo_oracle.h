@@ -48,8 +48,13 @@ enum {
     ORACLE_ARITH_DEVICE   = 1, /* the CUDA path's arithmetic restated op for op (fp32 X,
                                   squared norms + fp32-chunk dot products, FP64 lane sums,
                                   fixed butterfly order, svm_exp): used to check the GPU bit for bit */
-    ORACLE_ARITH_DEVICE_F64 = 2 /* the CUDA exact path (svmb200_set_exact: FP64 rows, squared
+    ORACLE_ARITH_DEVICE_F64 = 2, /* the CUDA exact path (svmb200_set_exact: FP64 rows, squared
                                   differences, per-lane FP64 sums, same butterfly, svm_exp) */
+    ORACLE_ARITH_DEVICE_U8 = 3   /* the CUDA path for uint8 input kept as uint8 (exact integer sums over the
+                                  features of the most frequent range, weighted FP64 sums over the rest; see
+                                  smo_oracle.c).  Needs oracle_u8_bind() on the raw training rows first; the
+                                  warm-start rebuild of f and the decision function use ORACLE_ARITH_DEVICE_F64,
+                                  as the device does */
 };
 
 typedef struct {
@@ -108,6 +113,13 @@ double oracle_device_sqdist_n(double na, double nb, double ab);
 double oracle_device_sqdist(const float *a, const float *b, size_t d);
 double oracle_device_kernel(const float *a, const float *b, size_t d, double gamma);
 double oracle_device_kernel_f64(const double *a, const double *b, size_t d, double gamma);
+/* ORACLE_ARITH_DEVICE_U8: bind the raw uint8 training rows [n x d] (min / range are taken from them), then
+ * oracle_smo_train(..., ORACLE_ARITH_DEVICE_U8, ...) on the same rows scaled.  row / piv index the bound rows. */
+void   oracle_u8_bind(const uint8_t *rows, size_t n, size_t d);
+void   oracle_u8_unbind(void);
+void   oracle_u8_layout(int *R, int64_t *M, int64_t *T);
+double oracle_u8_sqdist(size_t row, size_t piv);
+double oracle_u8_kernel(size_t row, size_t piv, double gamma);
 
 #ifdef __cplusplus
 }

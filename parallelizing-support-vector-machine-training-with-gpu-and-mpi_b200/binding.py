@@ -74,6 +74,8 @@ def load_library():
     L.svmb200_set_train_f64.argtypes = [vp, vp, vp, i64, i32, vp, vp]
     L.svmb200_set_train_scaled_f64.argtypes = [vp, vp, vp, i64, i32]
     L.svmb200_set_exact.argtypes = [vp, i32]
+    L.svmb200_set_storage.argtypes = [vp, i32]
+    L.svmb200_get_u8_layout.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
     L.svmb200_set_labels.argtypes = [vp, vp]
     L.svmb200_minmax_f64.argtypes = [vp, vp, i64, i32, vp, vp]
     L.svmb200_scale_f64.argtypes = [vp, vp, vp, vp, i64, i32]
@@ -86,6 +88,7 @@ def load_library():
     L.svmb200_kernel_row.argtypes = [vp, i64, dbl, i32, vp]
     L.svmb200_select_pair.argtypes = [vp, vp, vp, vp, i64, dbl, dbl, C.POINTER(i64), C.POINTER(i64)]
     L.svmb200_get_x_scaled.argtypes = [vp, vp]
+    L.svmb200_pair_update.argtypes = [vp, i32, i32, dbl, dbl, dbl, dbl, dbl, dbl, dbl, vp, C.POINTER(i32)]
     L.svmb200_set_tensor_cores.argtypes = [vp, i32, dbl]
     L.svmb200_debug_tc_dots.argtypes = [vp, vp, C.POINTER(i64)]
     L.svmb200_save_model.argtypes = [vp, C.c_char_p]
@@ -147,6 +150,17 @@ class Solver:
     def set_exact(self, enable: bool):
         """FP64 storage of X for the next set_train_* (the exact path); False = fp32 (default)."""
         self._ck(self.L.svmb200_set_exact(self.h, 1 if enable else 0), "set_exact")
+
+    STORAGE = {"f32": 0, "f64": 1, "u8": 2}
+
+    def set_storage(self, storage: str):
+        """How the next set_train_* keeps X: "f32" (default), "f64" (exact), "u8" (set_train_u8 only: the bytes themselves)."""
+        self._ck(self.L.svmb200_set_storage(self.h, self.STORAGE[storage]), "set_storage")
+
+    def u8_layout(self):
+        r, m, t, b = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        self._ck(self.L.svmb200_get_u8_layout(self.h, C.byref(r), C.byref(m), C.byref(t), C.byref(b)), "get_u8_layout")
+        return {"main_range": r.value, "main_features": m.value, "tail_features": t.value, "row_bytes": b.value}
 
     def set_train_u8(self, X, y):
         X = np.ascontiguousarray(X, dtype=np.uint8)
@@ -286,6 +300,14 @@ class Solver:
         self._ck(self.L.svmb200_select_pair(self.h, _ptr(alpha), _ptr(f), _ptr(y), alpha.size, C_, eps,
                                             C.byref(ih), C.byref(il)), "select_pair")
         return ih.value, il.value
+
+    def pair_update(self, y_high, y_low, a_high, a_low, b_high, b_low, K12, C_=10.0, eps=1e-12):
+        """calculate_U_V + the pair update as the solver runs them -> (dict, stop)."""
+        out = np.zeros(7)
+        stop = C.c_int32()
+        self._ck(self.L.svmb200_pair_update(self.h, y_high, y_low, a_high, a_low, b_high, b_low, K12, C_, eps, _ptr(out),
+                                            C.byref(stop)), "pair_update")
+        return dict(zip(("U", "V", "eta", "alpha_high", "alpha_low", "c_high", "c_low"), out.tolist())), stop.value
 
     def get_x_scaled(self):
         Xs = np.zeros((self.n, self.d), dtype=np.float32)

@@ -91,12 +91,15 @@ def main(argv=None):
 
     Xs, ys, als, idsv = res["sv"]
     if res["converged"]:
-        say(f"Converged at round {res['rounds'] - 1}, SV count = {len(idsv)}")
+        # the star program counts rounds from 0 (mpi_svm_main2.cpp:436,681,768), the tree program from 1 (mpi_svm_main3.cpp:562,568,750)
+        say(f"Converged at round {res['rounds'] - 1 if args.mode == 'star' else res['rounds']}, SV count = {len(idsv)}")
     else:
         say(f"Not converged after {res['rounds']} rounds, SV count = {len(idsv)}")
     say(f"Final b = {res['b']:.15f}")
     correct = 0
-    if rank == 0:
+    if rank == 0 and len(idsv) == 0:
+        say("Final model has no support vectors: nothing to predict with")
+    elif rank == 0:
         s.set_train_scaled(Xs, ys)
         s.set_model(als, res["b"])
         xt = s.scale_f64(np.ascontiguousarray(Xt, dtype=np.float64), mn, mx)

@@ -448,4 +448,13 @@ __global__ void select_pair_kernel(const double *__restrict__ alpha, const doubl
     }
 }
 
+// ---- introspection: the scalar part of one iteration (calculate_U_V + the pair update) exactly as the solver runs it
+__global__ void pair_update_kernel(int y_h, int y_l, double a_h, double a_l, double b_high, double b_low, double K12, double C, double eps,
+                                   double *__restrict__ out, int *__restrict__ stop)
+{
+    const PairStep r = pair_update(y_h, y_l, a_h, a_l, b_high, b_low, K12, C, eps);
+    out[0] = r.U; out[1] = r.V; out[2] = r.eta; out[3] = r.na_h; out[4] = r.na_l; out[5] = r.c_h; out[6] = r.c_l;
+    *stop = r.stop;
+}
+
 } // namespace svm

@@ -14,6 +14,7 @@
 #include "aux_kernels.cuh"
 #include "smo_kernel.cuh"
 #include "tc_decision.cuh"
+#include "u8_rows.cuh"
 
 using namespace svm;
 
@@ -43,8 +44,19 @@ struct svmb200_ctx {
     // training set
     long long n = 0;
     int d = 0, pitch4 = 0;
-    void *X = nullptr;          // fp32 rows, or FP64 rows when x_f64
-    bool exact_requested = false, x_f64 = false;
+    void *X = nullptr;          // fp32 rows, FP64 rows when x_f64, packed uint8 rows when x_u8
+    int storage_requested = SVMB200_STORAGE_F32;   // for the next svmb200_set_train_*
+    bool x_f64 = false, x_u8 = false;
+    // the rows the decision function works on (support-vector block, query rows): fp32 with fp32 storage, FP64 otherwise
+    bool dec_f64 = false;
+    int dec_pitch4 = 0;
+    // uint8 storage: layout of a packed row and its per-row norms (smo_kernel.cuh "uint8 rows")
+    int u8_mw = 0, u8_tw = 0, u8_R = 0, u8_M = 0, u8_T = 0;
+    double u8_wR = 0.0;
+    int *u8_nmain = nullptr, *u8_pos = nullptr, *u8_src = nullptr;
+    double *u8_ntail = nullptr, *u8_wt = nullptr;
+    void *Xdec = nullptr;       // uint8 storage: scaled FP64 copy of all rows, built when a warm start needs it
+    bool xdec_valid = false;
     int *y = nullptr;
     double *sqn = nullptr;      // |x_j|^2 formed with accumulation chunk sqn_chunk (0 = not computed)
     int sqn_chunk = 0;
@@ -61,8 +73,7 @@ struct svmb200_ctx {
     int cache_valid_cap = 0, cache_valid_chunk = 0;
     double cache_valid_gamma = 0.0;
     long long cache_counter = 0;
-    Rec *rec = nullptr;
-    int rec_blocks = 0;
+    Rec *rec = nullptr;                  // [2][SMO_MAX_RECS] exchange records + the abort word
     SmoResult *result = nullptr;
     int *trace = nullptr;
     int trace_alloc = 0, trace_count = 0;
@@ -80,6 +91,10 @@ struct svmb200_ctx {
     int model_nsv = 0;
     std::vector<int> model_y;   // labels of the support vectors (kept for svmb200_save_model)
     int sv_alloc = 0;
+    size_t svX_bytes = 0;          // capacity of svX (the row pitch may change between training sets)
+    std::vector<double> model_alpha;   // alpha of the support vectors (kept for svmb200_save_model)
+    bool have_params = false;      // params holds the values of the last svmb200_smo_train / svmb200_load_model
+    int cluster_size = 0;          // cluster size of the last SMO launch (2, or 1 when clusters could not be used)
 
     // tensor-core decision function (svmb200_set_tensor_cores)
     bool tc_predict = false;
@@ -230,6 +245,7 @@ void svmb200_destroy(svmb200_ctx *ctx)
     cudaFree(ctx->mailbox);
     cudaFree(ctx->svX); cudaFree(ctx->svcoef); cudaFree(ctx->scratch);
     cudaFree(ctx->work[0]); cudaFree(ctx->work[1]); cudaFree(ctx->svP);
+    cudaFree(ctx->u8_nmain); cudaFree(ctx->u8_pos); cudaFree(ctx->u8_src); cudaFree(ctx->u8_ntail); cudaFree(ctx->u8_wt); cudaFree(ctx->Xdec);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -244,16 +260,25 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
 {
     if (n <= 0 || d <= 0) FAIL(SVMB200_EINVAL, "n and d must be positive (n=%lld d=%d)", n, d);
     if (n >= 0x7fffffffLL) FAIL(SVMB200_ELIMIT, "n=%lld exceeds the 2^31-2 row limit", n);
-    const bool f64 = ctx->exact_requested;
-    const int pitch4 = f64 ? (d + 1) / 2 : (d + 3) / 4;          // 16-byte groups per row
-    if (pitch4 > max_pitch(f64))
-        FAIL(SVMB200_ELIMIT, "d=%d exceeds the %d-feature limit of the in-register pivot rows", d, f64 ? 832 : 1024);
+    const bool f64 = ctx->storage_requested == SVMB200_STORAGE_F64, u8 = ctx->storage_requested == SVMB200_STORAGE_U8;
+    const bool dec_f64 = f64 || u8;
+    const int dec_pitch4 = dec_f64 ? (d + 1) / 2 : (d + 3) / 4;  // 16-byte groups per row of the decision function's rows
+    if (dec_pitch4 > max_pitch(dec_f64))
+        FAIL(SVMB200_ELIMIT, "d=%d exceeds the %d-feature limit of the in-register pivot rows", d, dec_f64 ? 832 : 1024);
     CK(cudaSetDevice(ctx->device));
-    if (n != ctx->n || d != ctx->d || f64 != ctx->x_f64) {
+    if (n != ctx->n || d != ctx->d || f64 != ctx->x_f64 || u8 != ctx->x_u8 || u8) {
+        ctx->n = 0;                 // nothing is valid until every buffer below exists
+        ctx->d = 0;
+        ctx->have_train = false;
         if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->sqn) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
-            dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv))
+            dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv) || dev_free(ctx, ctx->svX) ||
+            dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn) || dev_free(ctx, ctx->u8_nmain) || dev_free(ctx, ctx->u8_ntail) ||
+            dev_free(ctx, ctx->Xdec))
             return SVMB200_ECUDA;
-        CK(cudaMalloc(&ctx->X, (size_t)n * pitch4 * 16));
+        ctx->sv_alloc = 0;          // the support-vector block was sized for the old row pitch
+        ctx->svX_bytes = 0;
+        const int pitch4 = u8 ? 0 : dec_pitch4;                  // uint8 rows: known (and X allocated) once the statistics are
+        if (!u8) CK(cudaMalloc(&ctx->X, (size_t)n * pitch4 * 16));
         CK(cudaMalloc(&ctx->y, (size_t)n * sizeof(int)));
         CK(cudaMalloc(&ctx->sqn, (size_t)n * sizeof(double)));
         CK(cudaMalloc(&ctx->f, (size_t)n * sizeof(double)));
@@ -261,10 +286,17 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
         CK(cudaMalloc(&ctx->cacheq, (size_t)n * sizeof(long long)));
         CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
         CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
+        if (u8) {
+            CK(cudaMalloc(&ctx->u8_nmain, (size_t)n * sizeof(int)));
+            CK(cudaMalloc(&ctx->u8_ntail, (size_t)n * sizeof(double)));
+        }
         ctx->n = n;
         ctx->d = d;
         ctx->pitch4 = pitch4;
         ctx->x_f64 = f64;
+        ctx->x_u8 = u8;
+        ctx->dec_f64 = dec_f64;
+        ctx->dec_pitch4 = dec_pitch4;
     }
     ctx->have_train = false;
     ctx->trained = false;
@@ -272,14 +304,15 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
     ctx->sqn_chunk = 0;
     ctx->model_ready = false;
     ctx->cache_valid = false;
+    ctx->xdec_valid = false;
     return 0;
 }
 
 // stage raw host rows in device scratch, compute statistics (optional), scale into dst
 template <typename T>
-static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool compute_stats, bool apply_stats, void *dst)
+static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool compute_stats, bool apply_stats, void *dst, bool dst_f64, int pitch4)
 {
-    const int d = ctx->d, pitch4 = ctx->pitch4;
+    const int d = ctx->d;
     const size_t raw_bytes = (size_t)rows * d * sizeof(T);
     const int parts = (int)std::min<long long>(ctx->num_sms, (rows + 63) / 64);
     const size_t part_bytes = compute_stats ? (size_t)2 * parts * d * sizeof(double) : 0;
@@ -297,7 +330,8 @@ static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool comput
     }
     const long long total = rows * pitch4;
     const int blocks = (int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16);
-    if (ctx->x_f64)
+    if (!dst) return 0;                         // statistics only (uint8 storage packs the raw rows itself)
+    if (dst_f64)
         scale_rows_kernel<T, double><<<blocks, 256, 0, ctx->stream>>>(raw, rows, d, pitch4, apply_stats ? ctx->minv : nullptr,
                                                                       apply_stats ? ctx->maxv : nullptr, static_cast<double *>(dst));
     else
@@ -308,14 +342,95 @@ static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool comput
     return 0;
 }
 
+// uint8 storage: how many words per lane the tail takes (a template parameter of the kernels: 2, 4 or 8)
+static int u8_qt_class(int tw) { return tw <= 64 ? 2 : tw <= 128 ? 4 : 8; }
+
+template <typename F>
+static cudaError_t dispatch_u8(int tw, F &&fn)
+{
+    switch (u8_qt_class(tw)) {
+    case 2: return fn.template operator()<8, 2>();
+    case 4: return fn.template operator()<8, 4>();
+    default: return fn.template operator()<8, 8>();
+    }
+}
+
+// uint8 storage: the statistics are on the device (ctx->minv / maxv) and the raw rows in scratch at `raw`.  Lays the row
+// out as [main class | tail] (smo_kernel.cuh "uint8 rows"), packs every row that way and forms the per-row norms.
+static int pack_u8_rows(svmb200_ctx *ctx, const unsigned char *raw, long long n)
+{
+    const int d = ctx->d;
+    std::vector<double> mn(d), mx(d);
+    CK(cudaMemcpyAsync(mn.data(), ctx->minv, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(mx.data(), ctx->maxv, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    // the main class: the most frequent non-zero range (the larger value wins a tie), if at least 32 features share it
+    std::vector<int> range(d);
+    int count[256] = {0};
+    for (int k = 0; k < d; ++k) { range[k] = (int)(mx[k] - mn[k]); count[range[k]]++; }
+    int R = 0;
+    for (int r = 1; r < 256; ++r)
+        if (count[r] > 0 && (R == 0 || count[r] >= count[R])) R = r;
+    if (R && count[R] < 32) R = 0;
+    std::vector<int> main_idx, tail_idx;
+    for (int k = 0; k < d; ++k) {
+        if (range[k] == 0) continue;              // a constant feature adds (u - p) = 0 to every distance
+        (range[k] == R ? main_idx : tail_idx).push_back(k);
+    }
+    const int M = (int)main_idx.size(), T = (int)tail_idx.size();
+    // both sections are padded with zero bytes (zero weights) to whole 128-byte slots: 32 lanes x one 4-byte word
+    const int mw = ((M + 3) / 4 + 31) & ~31, tw = ((T + 3) / 4 + 31) & ~31;
+    const int row_bytes = std::max(128, 4 * (mw + tw));
+    std::vector<int> src(row_bytes, -1), pos(d, -1);
+    std::vector<double> wt((size_t)std::max(tw, 1) * 4, 0.0);
+    for (int k = 0; k < M; ++k) { src[k] = main_idx[k]; pos[main_idx[k]] = k; }
+    for (int k = 0; k < T; ++k) {
+        src[4 * mw + k] = tail_idx[k];
+        pos[tail_idx[k]] = 4 * mw + k;
+        const double sk = 1.0 / (double)range[tail_idx[k]];
+        wt[k] = sk * sk;
+    }
+    const double sR = R ? 1.0 / (double)R : 0.0;
+    ctx->u8_R = R; ctx->u8_M = M; ctx->u8_T = T; ctx->u8_mw = mw; ctx->u8_tw = tw; ctx->u8_wR = sR * sR;
+    ctx->pitch4 = row_bytes / 16;
+    if (dev_free(ctx, ctx->u8_src) || dev_free(ctx, ctx->u8_pos) || dev_free(ctx, ctx->u8_wt) || dev_free(ctx, ctx->X)) return SVMB200_ECUDA;
+    CK(cudaMalloc(&ctx->u8_src, src.size() * sizeof(int)));
+    CK(cudaMalloc(&ctx->u8_pos, pos.size() * sizeof(int)));
+    CK(cudaMalloc(&ctx->u8_wt, wt.size() * sizeof(double)));
+    CK(cudaMalloc(&ctx->X, (size_t)n * row_bytes));
+    CK(cudaMemcpyAsync(ctx->u8_src, src.data(), src.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->u8_pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->u8_wt, wt.data(), wt.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    const long long words = n * (row_bytes / 4);
+    u8_pack_kernel<<<(int)std::min<long long>((words + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+        raw, n, d, row_bytes, ctx->u8_src, static_cast<unsigned char *>(ctx->X));
+    CK(cudaGetLastError());
+    CK(dispatch_u8(tw, [&]<int QM, int QT>() -> cudaError_t {
+        u8_norms_kernel<QM, QT><<<(unsigned)((n * 32 + 255) / 256), 256, 0, ctx->stream>>>(
+            static_cast<const unsigned char *>(ctx->X), n, row_bytes, mw, tw, ctx->u8_wt, ctx->u8_nmain, ctx->u8_ntail);
+        return cudaGetLastError();
+    }));
+    ctx->launches += 2;
+    CK(cudaStreamSynchronize(ctx->stream));      // src / pos / wt are host temporaries
+    return 0;
+}
+
 template <typename T>
 static int set_train(svmb200_ctx *ctx, const T *X, const int32_t *y, int64_t n, int32_t d, bool scale, double *min_out,
                      double *max_out)
 {
     if (!ctx) return SVMB200_EINVAL;
     if (!X || !y) FAIL(SVMB200_EINVAL, "X and y must not be NULL");
+    const bool u8 = ctx->storage_requested == SVMB200_STORAGE_U8;
+    if (u8 && !(std::is_same<T, uint8_t>::value && scale))
+        FAIL(SVMB200_ESTATE, "uint8 storage keeps the bytes of svmb200_set_train_u8: choose fp32 or FP64 storage for FP64 input");
     if (int rc = alloc_train(ctx, n, d)) return rc;
-    if (int rc = ingest<T>(ctx, X, n, scale, scale, ctx->X)) return rc;
+    if (int rc = ingest<T>(ctx, X, n, scale, scale, u8 ? nullptr : ctx->X, ctx->x_f64, ctx->pitch4)) return rc;
+    if (u8) {
+        const int parts = (int)std::min<long long>(ctx->num_sms, (n + 63) / 64);           // where ingest() staged the raw rows
+        const size_t raw_off = ((size_t)2 * parts * d * sizeof(double) + 255) & ~(size_t)255;
+        if (int rc = pack_u8_rows(ctx, static_cast<const unsigned char *>(ctx->scratch) + raw_off, n)) return rc;
+    }
     CK(cudaMemcpyAsync(ctx->y, y, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     if (scale) {
         if (min_out) CK(cudaMemcpyAsync(min_out, ctx->minv, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -361,7 +476,28 @@ extern "C" int svmb200_set_labels(svmb200_ctx *ctx, const int32_t *y)
 extern "C" int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable)
 {
     if (!ctx) return SVMB200_EINVAL;
-    ctx->exact_requested = enable != 0;
+    ctx->storage_requested = enable ? SVMB200_STORAGE_F64 : SVMB200_STORAGE_F32;
+    return SVMB200_OK;
+}
+
+// storage of X for the NEXT svmb200_set_train_*: fp32 rows, FP64 rows, or (svmb200_set_train_u8 only) the bytes themselves
+extern "C" int svmb200_set_storage(svmb200_ctx *ctx, int32_t storage)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (storage != SVMB200_STORAGE_F32 && storage != SVMB200_STORAGE_F64 && storage != SVMB200_STORAGE_U8)
+        FAIL(SVMB200_EINVAL, "storage must be SVMB200_STORAGE_F32, _F64 or _U8");
+    ctx->storage_requested = storage;
+    return SVMB200_OK;
+}
+
+extern "C" int svmb200_get_u8_layout(svmb200_ctx *ctx, int32_t *main_range, int32_t *main_features, int32_t *tail_features, int32_t *row_bytes)
+{
+    if (!ctx) return SVMB200_EINVAL;
+    if (!ctx->have_train || !ctx->x_u8) FAIL(SVMB200_ESTATE, "no training set in uint8 storage");
+    if (main_range) *main_range = ctx->u8_R;
+    if (main_features) *main_features = ctx->u8_M;
+    if (tail_features) *tail_features = ctx->u8_T;
+    if (row_bytes) *row_bytes = ctx->pitch4 * 16;
     return SVMB200_OK;
 }
 
@@ -465,14 +601,71 @@ static cudaError_t dispatch(const KernelKey &k, F &&fn)
 #undef SVM_F32_CASE
 }
 
-static cudaError_t launch_smo_any(const KernelKey &k, const SmoArgs &args, int grid, size_t smem, cudaStream_t stream)
+// cooperative launch (all CTAs co-resident: they spin on each other's records) in clusters of `cluster` CTAs
+template <typename K>
+static cudaError_t launch_persistent(K kernel, const SmoArgs &args, int grid, int threads, int cluster, size_t smem, cudaStream_t stream)
 {
-    return dispatch(k, [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
-        cudaError_t e = cudaFuncSetAttribute(smo_persistent_kernel<XT, Q, CH, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attrs[2];
+    attrs[0].id = cudaLaunchAttributeCooperative;
+    attrs[0].val.cooperative = 1;
+    attrs[1].id = cudaLaunchAttributeClusterDimension;
+    attrs[1].val.clusterDim.x = cluster;
+    attrs[1].val.clusterDim.y = 1;
+    attrs[1].val.clusterDim.z = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = 2;
+    if (cluster > 1) {
+        int max_clusters = 0;
+        e = cudaOccupancyMaxActiveClusters(&max_clusters, kernel, &cfg);
         if (e != cudaSuccess) return e;
-        void *kargs[] = {(void *)&args};
-        return cudaLaunchCooperativeKernel((void *)smo_persistent_kernel<XT, Q, CH, THREADS>, dim3(grid), dim3(THREADS), kargs, smem, stream);
-    });
+        if (max_clusters * cluster < grid) return cudaErrorCooperativeLaunchTooLarge;
+    }
+    return cudaLaunchKernelEx(&cfg, kernel, args);
+}
+
+// The SMO kernel's instantiations: fp32 rows in groups (256 threads) and FP64 rows; the one-row-per-step fp32 forms
+// (384 / 512 threads) exist in the profiling build only.
+static cudaError_t launch_smo_any(const KernelKey &k, const SmoArgs &args, int grid, int cluster, size_t smem, cudaStream_t stream)
+{
+    auto go = [&]<typename XT, int Q, int CH, int THREADS>() -> cudaError_t {
+        return launch_persistent(smo_persistent_kernel<XT, Q, CH, THREADS>, args, grid, THREADS, cluster, smem, stream);
+    };
+#ifdef SVM_TIMING
+    return dispatch(k, go);
+#else
+    if (k.f64) {
+        switch (k.Q) {
+        case 1: return go.template operator()<double, 1, 1, 384>();
+        case 2: return go.template operator()<double, 2, 1, 384>();
+        case 4: return go.template operator()<double, 4, 1, 384>();
+        case 7: return go.template operator()<double, 7, 1, 384>();
+        default:
+            if (k.threads == 256) return go.template operator()<double, 13, 1, 256>();
+            return go.template operator()<double, 13, 1, 384>();
+        }
+    }
+#define SVM_F32_SMO(QQ)                                                          \
+    switch (k.CH) {                                                              \
+    case 1: return go.template operator()<float, QQ, 1, 256>();                  \
+    case 2: return go.template operator()<float, QQ, 2, 256>();                  \
+    default: return go.template operator()<float, QQ, 4, 256>();                 \
+    }
+    switch (k.Q) {
+    case 1: SVM_F32_SMO(1)
+    case 2: SVM_F32_SMO(2)
+    case 4: SVM_F32_SMO(4)
+    case 7: SVM_F32_SMO(7)
+    default: SVM_F32_SMO(8)
+    }
+#undef SVM_F32_SMO
+#endif
 }
 
 template <typename XT, int Q, int CH, bool FULL>
@@ -562,7 +755,7 @@ static cudaError_t launch_sqnorm_any(KernelKey k, const float *X, long long n, i
 // squared norms of the fp32 training rows for accumulation chunk CH (recomputed only when CH changes)
 static int ensure_norms(svmb200_ctx *ctx, int CH)
 {
-    if (ctx->x_f64 || ctx->sqn_chunk == CH) return 0;
+    if (ctx->x_f64 || ctx->x_u8 || ctx->sqn_chunk == CH) return 0;
     KernelKey k{false, q_for_pitch(ctx->pitch4, false), CH, 512};
     cudaError_t e = launch_sqnorm_any(k, static_cast<const float *>(ctx->X), ctx->n, ctx->pitch4, ctx->sqn, ctx->stream);
     ctx->launches += 1;
@@ -574,6 +767,7 @@ static int ensure_norms(svmb200_ctx *ctx, int CH)
 // 8 warps x four rows per step (242 registers, no spills) + L2-resident share of X: 25.9 us/iteration at 60k; 12 warps x one row per
 // step (165 registers): 33.4; 16 warps (128 registers, spills): 35.4
 static const int SMO_DEFAULT_THREADS = 256;
+static const int SMO_U8_THREADS = 256;      // uint8 rows: 8 warps x groups of eight rows
 static const int DEFAULT_CHUNK = 4;   // fp32 storage of X dominates the error of K for every chunk (DESIGN.md "Numerics")
 
 static int resolve_chunk(int c)
@@ -587,10 +781,13 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
 {
     const int nsv = (int)ids.size();
     ctx->svP_valid = false;
-    if (nsv > ctx->sv_alloc) {
+    if (nsv > ctx->sv_alloc || (size_t)nsv * ctx->dec_pitch4 * 16 > ctx->svX_bytes) {
         if (dev_free(ctx, ctx->svX) || dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn)) return SVMB200_ECUDA;
+        ctx->sv_alloc = 0;
+        ctx->svX_bytes = 0;
         const int cap = std::max(nsv, 1024);
-        CK(cudaMalloc(&ctx->svX, (size_t)cap * ctx->pitch4 * 16));
+        CK(cudaMalloc(&ctx->svX, (size_t)cap * ctx->dec_pitch4 * 16));
+        ctx->svX_bytes = (size_t)cap * ctx->dec_pitch4 * 16;
         CK(cudaMalloc(&ctx->svcoef, (size_t)cap * sizeof(double)));
         CK(cudaMalloc(&ctx->svn, (size_t)cap * sizeof(double)));
         ctx->sv_alloc = cap;
@@ -601,8 +798,15 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
     if (int rc = ensure_scratch(ctx, (size_t)nsv * sizeof(int))) return rc;
     CK(cudaMemcpyAsync(ctx->scratch, ids.data(), (size_t)nsv * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->svcoef, coef.data(), (size_t)nsv * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    const long long total = (long long)nsv * ctx->pitch4;
-    gather_rows_kernel<<<(int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+    const long long total = (long long)nsv * ctx->dec_pitch4;
+    const int gblocks = (int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16);
+    if (ctx->x_u8) {            // the support vectors' bytes become scaled FP64 rows
+        u8_gather_scale_kernel<<<gblocks, 256, 0, ctx->stream>>>(static_cast<const unsigned char *>(ctx->X), ctx->pitch4 * 16, ctx->u8_pos, ctx->minv,
+                                                                   ctx->maxv, ctx->d, static_cast<const int *>(ctx->scratch), nsv, ctx->dec_pitch4,
+                                                                   static_cast<double *>(ctx->svX));
+        CK(cudaMemsetAsync(ctx->svn, 0, (size_t)nsv * sizeof(double), ctx->stream));
+    } else
+    gather_rows_kernel<<<gblocks, 256, 0, ctx->stream>>>(
         ctx->X, ctx->x_f64 ? nullptr : ctx->sqn, ctx->pitch4, static_cast<const int *>(ctx->scratch), nsv, ctx->svX, ctx->svn);
     ctx->launches += 1;
     CK(cudaGetLastError());
@@ -619,29 +823,45 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const int CH = resolve_chunk(params->accum_chunk);
     if (CH < 0) FAIL(SVMB200_EINVAL, "accum_chunk must be 0, 1, 2 or 4");
     if (params->max_iter < 1) FAIL(SVMB200_EINVAL, "max_iter must be >= 1");
+    if (ctx->shard_world > 1 && params->max_iter >= (1 << 21))
+        FAIL(SVMB200_ELIMIT, "row sharding numbers its exchanges with 21 bits: max_iter must be below %d", 1 << 21);
     CK(cudaSetDevice(ctx->device));
     const long long n = ctx->n;
     const int launches0 = ctx->launches;
 
     // persistent grid: one CTA per SM, fewer for tiny problems
-    const int Q = q_for_pitch(ctx->pitch4, ctx->x_f64);
+    const bool u8 = ctx->x_u8;
+    const int Q = u8 ? 8 : q_for_pitch(ctx->pitch4, ctx->x_f64);
+    const int QDEC = q_for_pitch(ctx->dec_pitch4, ctx->dec_f64);      // the decision kernels' row class (warm start)
     // fp32 rows: 8 warps taking rows in groups (SMO_DEFAULT_THREADS); FP64 rows: the same for the longest rows (Q = 13), else 12 warps, a row per step
-    int threads = ctx->x_f64 ? (Q == 13 && !getenv("SVMB200_F64_ONE_ROW") ? 256 : 384) : SMO_DEFAULT_THREADS;
+    int threads = u8 ? SMO_U8_THREADS : ctx->x_f64 ? (Q == 13 ? 256 : 384) : SMO_DEFAULT_THREADS;
+#ifdef SVM_TIMING      // measurement knobs exist in the profiling build only (libsvmb200_timing.so): the product reads no environment
+    if (ctx->x_f64 && Q == 13 && getenv("SVMB200_F64_ONE_ROW")) threads = 384;
     if (!ctx->x_f64)
-        if (const char *e = getenv("SVMB200_THREADS")) {   // tuning knob for profiles/sweep.py: 512 (384 at Q = 7) = a row per step
+        if (const char *e = getenv("SVMB200_THREADS")) {   // 512 (384 at Q = 7) = a row per step
             const int t = atoi(e);
             if (t == 256 || t == 512 || (t == 384 && Q == 7)) threads = t;
         }
+#endif
     const int warps = threads / 32;
-    const int rps = !ctx->x_f64 ? (threads <= 256 ? (Q == 8 ? 2 : 4) : 1) : (Q == 13 && threads == 256) ? 2 : 1;   // = smo_rows_per_step<XT, Q, THREADS>()
+    const int rps = u8 ? 8 : !ctx->x_f64 ? (threads <= 256 ? (Q == 8 ? 2 : 4) : 1) : (Q == 13 && threads == 256) ? 2 : 1;   // = smo_rows_per_step<XT, Q, THREADS>()
+    const int tailw = u8 ? ctx->u8_tw : 0;
     // ring depth: as many groups as fit, at most 4 (two at the MNIST shape: one in use, one in flight); a row per step: 4 rows at Q = 7, else 2
     int kslots = rps > 1 ? 4 : (Q == 7 && !ctx->x_f64) ? 4 : 2;
+#ifdef SVM_TIMING
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
-    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps) > (size_t)ctx->max_smem_optin) --kslots;
-    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps);
+#endif
+    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw) > (size_t)ctx->max_smem_optin) --kslots;
+    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
     const long long n_own = n * (ctx->shard_rank + 1) / ctx->shard_world - n * ctx->shard_rank / ctx->shard_world;
-    const int grid = (int)std::max<long long>(1, std::min<long long>(ctx->num_sms, (n_own + 7) / 8));
+    int grid = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS), (n_own + 7) / 8));
+    // thread-block clusters of two CTAs (neighbouring SMs) halve the records of the exchange; the grid is then even
+    int cluster = grid >= 2 ? 2 : 1;
+#ifdef SVM_TIMING
+    if (getenv("SVMB200_NO_CLUSTER")) cluster = 1;
+#endif
+    if (cluster == 2) grid &= ~1;
 
     // row cache
     int cache_cap = params->cache_rows;
@@ -657,11 +877,8 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         ctx->cacheK_elems = (size_t)cache_cap * n;
     }
 
-    if (grid > ctx->rec_blocks) {
-        if (dev_free(ctx, ctx->rec)) return SVMB200_ECUDA;
-        CK(cudaMalloc(&ctx->rec, (size_t)2 * grid * sizeof(Rec) + 256));
-        ctx->rec_blocks = grid;
-    }
+    const size_t rec_bytes = (size_t)2 * SMO_MAX_RECS * sizeof(Rec) + 256;     // two generations of records + the abort word
+    if (!ctx->rec) CK(cudaMalloc(&ctx->rec, rec_bytes));
     const int trace_cap = std::max(0, params->trace_cap);
     if (trace_cap > ctx->trace_alloc) {
         if (dev_free(ctx, ctx->trace)) return SVMB200_ECUDA;
@@ -674,7 +891,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
                       ctx->cache_valid_chunk == CH && ctx->cache_valid_gamma == params->gamma && ctx->shard_world == 1;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     if (int rc = ensure_norms(ctx, CH)) return rc;
-    CK(cudaMemsetAsync(ctx->rec, 0, (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 256, ctx->stream));
+    CK(cudaMemsetAsync(ctx->rec, 0, rec_bytes, ctx->stream));
     if (params->warm_start) {
         // f_i = sum_{alpha_j != 0} alpha_j y_j K(x_j, x_i) - y_i   (mpi_svm_main2.cpp:169-183)
         CK(cudaMemcpyAsync(ctx->alpha, alpha, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
@@ -689,7 +906,21 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         init_state_kernel<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(ctx->y, n, ctx->f, ctx->alpha, keep ? nullptr : ctx->cacheq, 0, 0);
         ctx->launches += 1;
         CK(cudaGetLastError());
-        CK(launch_decision_any(KernelKey{ctx->x_f64, Q, CH, 0}, ctx->X, n, ctx->svX, ctx->svn, ctx->svcoef, (int)nz.size(), ctx->pitch4, params->gamma, 0.0,
+        const void *Xd = ctx->X;
+        if (u8) {               // the decision kernel walks scaled FP64 rows: one copy of all rows, kept until the next upload
+            if (!ctx->Xdec) CK(cudaMalloc(&ctx->Xdec, (size_t)n * ctx->dec_pitch4 * 16));
+            if (!ctx->xdec_valid) {
+                const long long total = n * ctx->dec_pitch4;
+                u8_gather_scale_kernel<<<(int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+                    static_cast<const unsigned char *>(ctx->X), ctx->pitch4 * 16, ctx->u8_pos, ctx->minv, ctx->maxv, ctx->d, nullptr, n,
+                    ctx->dec_pitch4, static_cast<double *>(ctx->Xdec));
+                ctx->launches += 1;
+                CK(cudaGetLastError());
+                ctx->xdec_valid = true;
+            }
+            Xd = ctx->Xdec;
+        }
+        CK(launch_decision_any(KernelKey{ctx->dec_f64, QDEC, CH, 0}, Xd, n, ctx->svX, ctx->svn, ctx->svcoef, (int)nz.size(), ctx->dec_pitch4, params->gamma, 0.0,
                                ctx->y, ctx->f, ctx->stream));
         ctx->launches += 1;
     } else {
@@ -699,10 +930,11 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
 
     SmoArgs a{};
-    a.X = ctx->X; a.sqn = ctx->x_f64 ? nullptr : ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
+    a.X = ctx->X; a.sqn = (ctx->x_f64 || u8) ? nullptr : ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
+    a.nmain = ctx->u8_nmain; a.ntail = ctx->u8_ntail; a.wt = ctx->u8_wt; a.mw = ctx->u8_mw; a.tw = ctx->u8_tw; a.wR = ctx->u8_wR;
     a.cacheq = cache_cap > 0 ? ctx->cacheq : nullptr;
     a.cacheK = ctx->cacheK; a.rec = ctx->rec;
-    a.arrive = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * ctx->rec_blocks * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
+    a.abort_word = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * SMO_MAX_RECS * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
     a.n = n; a.pitch4 = ctx->pitch4; a.kslots = kslots; a.cache_cap = cache_cap; a.trace_cap = trace_cap;
     a.max_iter = params->max_iter;
     a.cache_counter0 = keep ? ctx->cache_counter : 0;
@@ -715,7 +947,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         // only with the four-rows-per-step pass: with a row per step the SM side, not HBM, bounds the pass.
         const double x_bytes = (double)n_own * ctx->pitch4 * 16;
         double l2_keep_budget = 80.0 * 1024 * 1024;
+#ifdef SVM_TIMING
         if (const char *e = getenv("SVMB200_L2KEEP_MB")) l2_keep_budget = atof(e) * 1024 * 1024;
+#endif
         int persist = params->l2_persist;
         if (persist < 0) persist = rps > 1;
         if (x_bytes <= 96.0 * 1024 * 1024) { a.policy_stream = L2_EVICT_NORMAL; a.policy_keep = L2_EVICT_NORMAL; }
@@ -738,8 +972,31 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
 #endif
 
+    if (ctx->shard_world > 1) {
+        // the GPUs of a row-sharded run meet on the device before the timed launch: every process reaches this point at
+        // its own time (host skew of a millisecond or more), and the persistent kernels run in lock step once all are there
+        PeerFlags pf{};
+        for (int p = 0; p < 8; ++p) pf.peer[p] = ctx->peer_mailbox[p] ? reinterpret_cast<unsigned long long *>(ctx->peer_mailbox[p] + 16) : nullptr;
+        peer_rendezvous_kernel<<<1, 32, 0, ctx->stream>>>(pf, ctx->shard_rank, ctx->shard_world, (unsigned long long)a.epoch);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    CK(launch_smo_any(KernelKey{ctx->x_f64, Q, CH, threads}, a, grid, smem, ctx->stream));
+    auto launch = [&](int cl) -> cudaError_t {
+        if (u8)
+            return dispatch_u8(ctx->u8_tw, [&]<int QM, int QT>() -> cudaError_t {
+                return launch_persistent(smo_persistent_kernel<unsigned char, QM, QT, SMO_U8_THREADS>, a, grid, SMO_U8_THREADS, cl, smem, ctx->stream);
+            });
+        return launch_smo_any(KernelKey{ctx->x_f64, Q, CH, threads}, a, grid, cl, smem, ctx->stream);
+    };
+    cudaError_t le = launch(cluster);
+    if (le != cudaSuccess && cluster > 1) {      // this device cannot co-schedule the clusters: same kernel, cluster size 1
+        (void)cudaGetLastError();
+        cluster = 1;
+        le = launch(cluster);
+    }
+    CK(le);
+    ctx->cluster_size = cluster;
     ctx->launches += 1;
     CK(cudaEventRecord(ctx->ev2, ctx->stream));
 
@@ -752,6 +1009,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     ctx->b = *b;
     ctx->params = *params;
     ctx->params.accum_chunk = CH;
+    ctx->have_params = true;
     ctx->alpha_host.assign(alpha, alpha + n);
     ctx->sv_ids.clear();
     for (long long i = 0; i < n; ++i)            // get_SV_indices, main3.cpp:297-304
@@ -793,8 +1051,8 @@ extern "C" int svmb200_shard_setup(svmb200_ctx *ctx, int32_t rank, int32_t world
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     CK(cudaSetDevice(ctx->device));
     if (ctx->mailbox) FAIL(SVMB200_ESTATE, "svmb200_shard_setup called twice");
-    CK(cudaMalloc(&ctx->mailbox, (size_t)2 * 8 * sizeof(Rec)));
-    CK(cudaMemset(ctx->mailbox, 0, (size_t)2 * 8 * sizeof(Rec)));
+    CK(cudaMalloc(&ctx->mailbox, (size_t)(2 * 8 + 1) * sizeof(Rec)));      // [2][8] records + 8 rendezvous flags
+    CK(cudaMemset(ctx->mailbox, 0, (size_t)(2 * 8 + 1) * sizeof(Rec)));
     cudaIpcMemHandle_t h;
     CK(cudaIpcGetMemHandle(&h, ctx->mailbox));
     memcpy(handle_out, &h, sizeof h);
@@ -829,7 +1087,9 @@ extern "C" int svmb200_set_model(svmb200_ctx *ctx, const double *alpha, double b
     if (!ctx || !alpha) return SVMB200_EINVAL;
     if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set");
     CK(cudaSetDevice(ctx->device));
-    if (!ctx->trained) { svmb200_default_params(&ctx->params); ctx->params.accum_chunk = DEFAULT_CHUNK; }
+    // gamma, sv_tol and the arithmetic are those of the last svmb200_smo_train on this context (a new upload does not
+    // forget them); a context that never trained takes the defaults
+    if (!ctx->have_params) { svmb200_default_params(&ctx->params); ctx->params.accum_chunk = DEFAULT_CHUNK; ctx->have_params = true; }
     ctx->alpha_host.assign(alpha, alpha + ctx->n);
     ctx->b = b;
     ctx->sv_ids.clear();
@@ -864,16 +1124,16 @@ extern "C" int svmb200_save_model(svmb200_ctx *ctx, const char *path)
     const int nsv = ctx->model_nsv;
     ModelHeader h{};
     memcpy(h.magic, "SVMB200M", 8);
-    h.version = 2; h.x_f64 = ctx->x_f64 ? 1 : 0; h.d = ctx->d; h.pitch4 = ctx->pitch4; h.n_sv = nsv; h.accum_chunk = ctx->params.accum_chunk;
+    h.version = 2; h.x_f64 = ctx->dec_f64 ? 1 : 0; h.d = ctx->d; h.pitch4 = ctx->dec_pitch4; h.n_sv = nsv; h.accum_chunk = ctx->params.accum_chunk;
     h.have_stats = ctx->have_stats ? 1 : 0; h.gamma = ctx->params.gamma; h.b = ctx->b; h.sv_tol = ctx->params.sv_tol;
     std::vector<double> mn(ctx->d), mx(ctx->d), al(nsv);
-    std::vector<float> rows((size_t)nsv * ctx->pitch4 * 4);
+    std::vector<float> rows((size_t)nsv * ctx->dec_pitch4 * 4);
     if (ctx->have_stats) {
         CK(cudaMemcpy(mn.data(), ctx->minv, (size_t)ctx->d * sizeof(double), cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(mx.data(), ctx->maxv, (size_t)ctx->d * sizeof(double), cudaMemcpyDeviceToHost));
     }
     if (nsv) CK(cudaMemcpy(rows.data(), ctx->svX, rows.size() * sizeof(float), cudaMemcpyDeviceToHost));
-    for (int k = 0; k < nsv; ++k) al[k] = ctx->alpha_host[ctx->sv_ids[k]];
+    for (int k = 0; k < nsv; ++k) al[k] = ctx->model_alpha[k];
     FILE *f = fopen(path, "wb");
     if (!f) FAIL(SVMB200_EINVAL, "cannot open %s for writing", path);
     bool ok = fwrite(&h, sizeof h, 1, f) == 1;
@@ -907,9 +1167,10 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
     // the context now holds a model only: any training set is dropped
     if (dev_free(ctx, ctx->X) || dev_free(ctx, ctx->y) || dev_free(ctx, ctx->sqn) || dev_free(ctx, ctx->f) || dev_free(ctx, ctx->alpha) ||
         dev_free(ctx, ctx->cacheq) || dev_free(ctx, ctx->minv) || dev_free(ctx, ctx->maxv) || dev_free(ctx, ctx->svX) ||
-        dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn))
+        dev_free(ctx, ctx->svcoef) || dev_free(ctx, ctx->svn) || dev_free(ctx, ctx->u8_nmain) || dev_free(ctx, ctx->u8_ntail) || dev_free(ctx, ctx->Xdec))
         return SVMB200_ECUDA;
-    ctx->n = 0; ctx->d = d; ctx->pitch4 = h.pitch4; ctx->x_f64 = h.x_f64 != 0; ctx->have_train = false; ctx->sqn_chunk = 0; ctx->sv_alloc = std::max(nsv, 1);
+    ctx->n = 0; ctx->d = d; ctx->pitch4 = h.pitch4; ctx->x_f64 = h.x_f64 != 0; ctx->x_u8 = false; ctx->dec_f64 = ctx->x_f64; ctx->dec_pitch4 = h.pitch4; ctx->have_train = false; ctx->sqn_chunk = 0; ctx->sv_alloc = std::max(nsv, 1);
+    ctx->svX_bytes = (size_t)ctx->sv_alloc * h.pitch4 * 16;
     CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
     CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
     ctx->svP_valid = false;
@@ -936,7 +1197,7 @@ extern "C" int svmb200_load_model(svmb200_ctx *ctx, const char *path)
     svmb200_default_params(&ctx->params);
     ctx->params.gamma = h.gamma; ctx->params.sv_tol = h.sv_tol; ctx->params.accum_chunk = h.accum_chunk;
     ctx->b = h.b; ctx->have_stats = h.have_stats != 0;
-    ctx->sv_ids = ids; ctx->model_y = ys; ctx->alpha_host.clear();
+    ctx->sv_ids = ids; ctx->model_y = ys; ctx->model_alpha = al; ctx->alpha_host.clear(); ctx->have_params = true;
     ctx->model_nsv = nsv; ctx->model_ready = true; ctx->trained = true;
     return SVMB200_OK;
 }
@@ -972,7 +1233,7 @@ static int launch_tc_scores(svmb200_ctx *ctx, const float *Xq, const double *qn,
                             const float *svX, const double *svn, const double *svcoef, int nsv, unsigned char *svP, double init,
                             double *dscores, float *dots)
 {
-    const int pitch = ctx->pitch4 * 4;
+    const int pitch = ctx->dec_pitch4 * 4;
     const int kblocks = (ctx->d + TC_KB - 1) / TC_KB;
     const int blocks = ctx->num_sms * 8;
     if (!svP) {
@@ -1017,7 +1278,7 @@ extern "C" int svmb200_debug_tc_dots(svmb200_ctx *ctx, float *dots, int64_t *rec
     if (!ctx) return SVMB200_EINVAL;
     if (rechecked) *rechecked = ctx->tc_rechecked;
     if (!dots) return SVMB200_OK;
-    if (!ctx->have_train || ctx->x_f64) FAIL(SVMB200_ESTATE, "needs an fp32 training set");
+    if (!ctx->have_train || ctx->x_f64 || ctx->x_u8) FAIL(SVMB200_ESTATE, "needs an fp32 training set");
     CK(cudaSetDevice(ctx->device));
     const long long rows = std::min<long long>(ctx->n, TC_M);
     if (int rc = ensure_norms(ctx, DEFAULT_CHUNK)) return rc;
@@ -1058,7 +1319,11 @@ static int ensure_model(svmb200_ctx *ctx)
     CK(cudaMemcpyAsync(y_host.data(), ctx->y, (size_t)ctx->n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->model_y.resize(ctx->sv_ids.size());
-    for (size_t k = 0; k < ctx->model_y.size(); ++k) ctx->model_y[k] = y_host[ctx->sv_ids[k]];
+    ctx->model_alpha.resize(ctx->sv_ids.size());
+    for (size_t k = 0; k < ctx->model_y.size(); ++k) {
+        ctx->model_y[k] = y_host[ctx->sv_ids[k]];
+        ctx->model_alpha[k] = ctx->alpha_host[ctx->sv_ids[k]];
+    }
     if (int rc = ensure_norms(ctx, ctx->params.accum_chunk)) return rc;
     if (int rc = build_sv_block(ctx, ctx->sv_ids, ctx->alpha_host.data(), ctx->model_y)) return rc;
     ctx->model_nsv = (int)ctx->sv_ids.size();
@@ -1075,12 +1340,12 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     if (!X || m <= 0) FAIL(SVMB200_EINVAL, "X must not be NULL and m must be positive");
     if (scale && !ctx->have_stats) FAIL(SVMB200_ESTATE, "the training set was uploaded pre-scaled: use svmb200_predict_scaled_f64");
     CK(cudaSetDevice(ctx->device));
-    const int pitch4 = ctx->pitch4;
+    const int pitch4 = ctx->dec_pitch4;
     if (int rc = ensure_model(ctx)) return rc;
 
     // one grow-only work area: query rows | scores | labels + counter | (tensor cores: norms | list + counter | packed rows)
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    const bool use_tc = ctx->tc_predict && !ctx->x_f64 && ctx->model_nsv > 0;
+    const bool use_tc = ctx->tc_predict && !ctx->dec_f64 && ctx->model_nsv > 0;
     const size_t o_x = 0, o_scores = o_x + up((size_t)m * pitch4 * 16), o_y = o_scores + up((size_t)m * sizeof(double)),
                  o_qn = o_y + up(((size_t)m + 1) * sizeof(int)), o_list = o_qn + (use_tc ? up((size_t)m * sizeof(double)) : 0),
                  o_panel = o_list + (use_tc ? up(((size_t)m + 1) * sizeof(int)) : 0), o_part = o_panel + (use_tc ? tc_panel_bytes(ctx, m) : 0),
@@ -1090,8 +1355,8 @@ static int predict_impl(svmb200_ctx *ctx, const T *X, const int32_t *y_test, int
     void *Xq = w + o_x;
     double *dscores = reinterpret_cast<double *>(w + o_scores);
     int *dy = reinterpret_cast<int *>(w + o_y), *dcorrect = dy + m;
-    if (int rc = ingest<T>(ctx, X, m, false, scale, Xq)) return rc;
-    const KernelKey key{ctx->x_f64, q_for_pitch(pitch4, ctx->x_f64), ctx->params.accum_chunk, 0};
+    if (int rc = ingest<T>(ctx, X, m, false, scale, Xq, ctx->dec_f64, pitch4)) return rc;
+    const KernelKey key{ctx->dec_f64, q_for_pitch(pitch4, ctx->dec_f64), ctx->params.accum_chunk, 0};
     if (use_tc) {
         // tensor cores first (TF32x3, approximate), then the exact kernel for every row whose |score| is under the threshold
         const int nsv = ctx->model_nsv;
@@ -1193,8 +1458,17 @@ int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_
     if (int rc = ensure_norms(ctx, CH)) return rc;
     if (int rc = ensure_scratch(ctx, (size_t)ctx->n * sizeof(double))) return rc;
     double *out = static_cast<double *>(ctx->scratch);
-    cudaError_t e = launch_krow_any(KernelKey{ctx->x_f64, q_for_pitch(ctx->pitch4, ctx->x_f64), CH, 0}, ctx->X, ctx->x_f64 ? nullptr : ctx->sqn,
-                                    ctx->n, ctx->pitch4, i, gamma, out, ctx->stream);
+    cudaError_t e;
+    if (ctx->x_u8)
+        e = dispatch_u8(ctx->u8_tw, [&]<int QM, int QT>() -> cudaError_t {
+            u8_kernel_row_kernel<QM, QT><<<(unsigned)((ctx->n * 32 + 255) / 256), 256, 0, ctx->stream>>>(
+                static_cast<const unsigned char *>(ctx->X), ctx->n, ctx->pitch4 * 16, ctx->u8_mw, ctx->u8_tw, ctx->u8_wt, ctx->u8_wR, ctx->u8_nmain,
+                ctx->u8_ntail, i, gamma, out);
+            return cudaGetLastError();
+        });
+    else
+        e = launch_krow_any(KernelKey{ctx->x_f64, q_for_pitch(ctx->pitch4, ctx->x_f64), CH, 0}, ctx->X, ctx->x_f64 ? nullptr : ctx->sqn,
+                            ctx->n, ctx->pitch4, i, gamma, out, ctx->stream);
     ctx->launches += 1;
     CK(e);
     CK(cudaMemcpyAsync(row, out, (size_t)ctx->n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1226,11 +1500,43 @@ int svmb200_select_pair(svmb200_ctx *ctx, const double *alpha, const double *f, 
     return SVMB200_OK;
 }
 
+int svmb200_pair_update(svmb200_ctx *ctx, int32_t y_high, int32_t y_low, double alpha_high, double alpha_low, double b_high,
+                        double b_low, double K12, double C, double eps, double *out7, int32_t *stop)
+{
+    if (!ctx || !out7 || !stop) return SVMB200_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    if (int rc = ensure_scratch(ctx, 8 * sizeof(double))) return rc;
+    double *dout = static_cast<double *>(ctx->scratch);
+    int *dstop = reinterpret_cast<int *>(dout + 7);
+    pair_update_kernel<<<1, 1, 0, ctx->stream>>>(y_high, y_low, alpha_high, alpha_low, b_high, b_low, K12, C, eps, dout, dstop);
+    ctx->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out7, dout, 7 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(stop, dstop, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SVMB200_OK;
+}
+
 int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs)
 {
     if (!ctx || !Xs) return SVMB200_EINVAL;
     if (!ctx->have_train) FAIL(SVMB200_ESTATE, "no training set");
     CK(cudaSetDevice(ctx->device));
+    if (ctx->x_u8) {        // uint8 storage: the scaled FP64 rows, rounded to fp32
+        const size_t bytes = (size_t)ctx->n * ctx->dec_pitch4 * 16;
+        if (int rc = ensure_work(ctx, 1, bytes)) return rc;
+        const long long total = ctx->n * ctx->dec_pitch4;
+        u8_gather_scale_kernel<<<(int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+            static_cast<const unsigned char *>(ctx->X), ctx->pitch4 * 16, ctx->u8_pos, ctx->minv, ctx->maxv, ctx->d, nullptr, ctx->n, ctx->dec_pitch4,
+            static_cast<double *>(ctx->work[1]));
+        CK(cudaGetLastError());
+        std::vector<double> tmp((size_t)ctx->n * ctx->d);
+        CK(cudaMemcpy2DAsync(tmp.data(), (size_t)ctx->d * sizeof(double), ctx->work[1], (size_t)ctx->dec_pitch4 * 16, (size_t)ctx->d * sizeof(double),
+                             (size_t)ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (size_t k = 0; k < tmp.size(); ++k) Xs[k] = (float)tmp[k];
+        return SVMB200_OK;
+    }
     if (ctx->x_f64) {       // exact storage: hand back the rows rounded to fp32
         std::vector<double> tmp((size_t)ctx->n * ctx->d);
         CK(cudaMemcpy2D(tmp.data(), (size_t)ctx->d * sizeof(double), ctx->X, (size_t)ctx->pitch4 * 16, (size_t)ctx->d * sizeof(double),

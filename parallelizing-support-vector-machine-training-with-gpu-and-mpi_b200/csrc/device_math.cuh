@@ -116,9 +116,11 @@ __device__ __forceinline__ double sqdist_from_dot(double na, double nb, double a
 template <typename XT> struct RowVec;
 template <> struct RowVec<float> { using type = float4; };
 template <> struct RowVec<double> { using type = double2; };
+template <> struct RowVec<unsigned char> { using type = uint4; };       // uint8 rows are walked in 4-byte words by code of their own
 template <typename V> __device__ __forceinline__ V vec_zero();
 template <> __device__ __forceinline__ float4 vec_zero<float4>() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 template <> __device__ __forceinline__ double2 vec_zero<double2>() { return make_double2(0.0, 0.0); }
+template <> __device__ __forceinline__ uint4 vec_zero<uint4>() { return make_uint4(0u, 0u, 0u, 0u); }
 
 template <int CH>
 __device__ __forceinline__ void accum_pair(const float4 &v, const float4 &p, double &acc) { accum_dot<CH>(v, p, acc); }

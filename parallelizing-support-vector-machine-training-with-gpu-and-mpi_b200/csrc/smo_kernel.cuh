@@ -53,8 +53,8 @@ struct SmoArgs {
     double *alpha;
     long long *cacheq;     // per row: allocation number of its cached kernel row, or -1
     double *cacheK;        // [cache_cap][n] FP64 kernel rows
-    Rec *rec;              // [2][grid]
-    unsigned *arrive;      // arrival counter of the record exchange (zeroed before the launch)
+    Rec *rec;              // [2][SMO_MAX_RECS] records of the exchange, zeroed before the launch
+    unsigned *abort_word;  // set when a wait was given up (a peer GPU is gone): ends every other wait; zeroed before the launch
     int *trace;            // [trace_cap][2]
     SmoResult *result;
     long long n;
@@ -72,9 +72,15 @@ struct SmoArgs {
     int peers;                          // GPUs sharing the rows
     int rank;                           // this GPU
     long long row_begin, row_end;       // rows owned by this GPU (X is replicated, state is global-sized)
-    Rec *mailbox;                       // [2][peers] local mailbox written by peers
+    Rec *mailbox;                       // [2][8] local mailbox written by peers
     Rec *peer_mailbox[8];               // peers' mailboxes (peer-mapped device pointers; [rank] is the local one)
     int epoch;                          // launch number, folded into the mailbox words so that stale records never match
+    // ---- uint8 rows (storage "u8"): X is [n][pitch4 * 16] bytes = mw words of the main class | tw words of the tail | padding
+    const int *nmain;                   // [n] integer squared norms over the main class
+    const double *ntail;                // [n] weighted squared norms over the tail
+    const double *wt;                   // [tw * 4] weights (1 / range)^2 of the tail features (0 for padding bytes)
+    int mw, tw;                         // 4-byte words of a row in the main class / in the tail, each padded to a multiple of 32
+    double wR;                          // weight of the main class
     long long *timing;                  // optional [iterations][8] clock64 stamps of CTA 0 (profiling builds only)
     int timing_cap;
 };
@@ -86,7 +92,7 @@ struct SmoArgs {
 template <typename XT, int Q, int THREADS>
 constexpr int smo_rows_per_step()
 {
-    return (sizeof(XT) == 4 && THREADS <= 256) ? (Q == 8 ? 2 : 4) : (sizeof(XT) == 8 && Q == 13 && THREADS == 256) ? 2 : 1;
+    return sizeof(XT) == 1 ? 8 : (sizeof(XT) == 4 && THREADS <= 256) ? (Q == 8 ? 2 : 4) : (sizeof(XT) == 8 && Q == 13 && THREADS == 256) ? 2 : 1;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -140,6 +146,51 @@ __device__ __forceinline__ void group_dot2(const unsigned char *grp, int row_byt
             accum_pair<CH>(v, pv.l[NG - 1], P[RPS + r]);
         }
     }
+}
+
+// ---- uint8 rows.  For integer-valued input the reference's scaled difference (code/main3.cpp:74-89, :97-100) is
+// (a_k - b_k)^2 = (u_k - p_k)^2 / range_k^2 with integer u, p, range, so the raw bytes are kept and
+//     d2 = S_main * w_R + tail
+//   S_main = sum over the features whose range is the most frequent one (R) of (u_k - p_k)^2, an exact integer formed as
+//            |u|^2 + |p|^2 - 2 u.p with four products per IDP4A;
+//   tail   = (N(u) + N(p)) - 2 D(u, p) over the other non-constant features, D(u, p) = sum_k u_k * (w_k p_k) in FP64:
+//            lane l owns the words l, l + 32, ... of the tail, adds its bytes in order with fma, and the lane sums are
+//            combined in xor-butterfly order; N(u) = D(u, u), so duplicates are at distance exactly 0.
+// A byte becomes a double by placing it in the mantissa of 2^52 and subtracting 2^52 (exact, no conversion unit).
+__device__ __forceinline__ double u8_to_f64(unsigned w, int c)
+{
+    return __hiloint2double(0x43300000, (int)__byte_perm(w, 0u, 0x4440u + (unsigned)c)) - 4503599627370496.0;
+}
+// K(row, piv) straight from global memory by one warp (same sums in the same order as the pass)
+template <int QM, int QT>
+__device__ __forceinline__ double u8_kernel_value(const unsigned char *X, int row_bytes, int mw, int tw, const double *__restrict__ wt, double wR,
+                                                  const int *__restrict__ nmain, const double *__restrict__ ntail, long long row, long long piv,
+                                                  double gamma, int lane)
+{
+    const unsigned *xr = reinterpret_cast<const unsigned *>(X + (size_t)row * row_bytes);
+    const unsigned *xp = reinterpret_cast<const unsigned *>(X + (size_t)piv * row_bytes);
+    int dot = 0;
+#pragma unroll
+    for (int i = 0; i < QM; ++i) {
+        const int w = i * 32 + lane;
+        if (w < mw) dot = __dp4a(__ldg(xr + w), __ldg(xp + w), (unsigned)dot);
+    }
+    dot = __reduce_add_sync(FULL, dot);
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < QT; ++i) {
+        const int w = i * 32 + lane;
+        if (w < tw) {
+            const unsigned ur = __ldg(xr + mw + w), up = __ldg(xp + mw + w);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc = fma(u8_to_f64(ur, c), wt[4 * w + c] * u8_to_f64(up, c), acc);
+        }
+    }
+    acc = warp_sum_butterfly(acc);
+    const int S = nmain[row] + nmain[piv] - 2 * dot;
+    double tail = (ntail[row] + ntail[piv]) - 2.0 * acc;
+    if (tail < 0.0) tail = 0.0;
+    return svm_exp(-gamma * fma((double)S, wR, tail));
 }
 
 // membership tests of calc_i_high / calc_i_low (code/main3.cpp:115,134)
@@ -223,16 +274,58 @@ __device__ __forceinline__ void best_merge(LocalBest &b, const Best &lo, const B
     if (better_max(hi.f, hi.idx, b.hi.f, b.hi.idx)) b.hi = hi;
 }
 
+// The scalar part of an iteration, code/main3.cpp:235-270 operation for operation: s, eta, calculate_U_V (:145-159),
+// the clipped alpha_low', alpha_high', and the two coefficients of the f update.  Every CTA runs it redundantly on the
+// same inputs (identical bits everywhere, so nothing is broadcast).  stop: 0 = go on, 2 = infeasible U and V (:246),
+// 3 = non positive eta (:253).
+struct PairStep { double U, V, eta, na_h, na_l, c_h, c_l; int stop; };
+__device__ __forceinline__ PairStep pair_update(int y_h, int y_l, double a_h, double a_l, double b_high, double b_low, double K12,
+                                                double C, double eps)
+{
+    PairStep r;
+    const int s = y_h * y_l;
+    const double K11 = 1.0, K22 = 1.0;                    // exp(-gamma * 0)
+    r.eta = K11 + K22 - 2.0 * K12;
+    if (s == -1) {
+        const double u = a_l - a_h, v = C + a_l - a_h;
+        r.U = (0.0 < u) ? u : 0.0;
+        r.V = (v < C) ? v : C;
+    } else {
+        const double u = a_l + a_h - C, v = a_l + a_h;
+        r.U = (0.0 < u) ? u : 0.0;
+        r.V = (v < C) ? v : C;
+    }
+    r.na_h = a_h; r.na_l = a_l; r.c_h = 0.0; r.c_l = 0.0;
+    r.stop = 0;
+    if (!(r.U <= r.V + 1e-12)) { r.stop = 2; return r; }  // main3.cpp:246
+    if (r.eta <= eps) { r.stop = 3; return r; }            // main3.cpp:253
+    double na_l = a_l + y_l * (b_high - b_low) / r.eta;    // main3.cpp:259
+    if (na_l > r.V) na_l = r.V;
+    if (na_l < r.U) na_l = r.U;
+    r.na_l = na_l;
+    r.na_h = a_h + s * (a_l - na_l);                       // main3.cpp:266
+    r.c_h = (r.na_h - a_h) * y_h;                          // delta_alpha_i_high * y[i_high]
+    r.c_l = (r.na_l - a_l) * y_l;
+    return r;
+}
+
 // ---- the record exchange ---------------------------------------------------------------------
-// Every CTA stores its record, then adds 1 to an arrival counter.  ONE thread per CTA spins on the
-// counter (148 pollers of one 4-byte word; having all 148 x 148 record readers spin instead measured
-// ~10 us per exchange in L2 queueing); when the count is complete thread t reads CTA t's record.
-// No fence orders the record against the counter.  Instead a record is 16 words of 8 bytes, each
-// {32 data bits, 32-bit exchange number}: an aligned 8-byte access is single-copy atomic, so a word
-// that shows the right number also shows its data, and a reader that is too early simply re-reads.
+// The one grid-wide synchronisation of an iteration, in four hops:
+//   1. CTA: warp winners (REDUX) -> shared memory -> warp 0 folds them;
+//   2. cluster (two CTAs on neighbouring SMs): the non-leader CTA writes its winners into the leader's shared memory
+//      (distributed shared memory, st.shared::cluster) and arrives on the leader's mbarrier; the leader folds the two;
+//   3. grid: the leader stores ONE 128-byte record per cluster (74 on a B200) and polls the others' records directly --
+//      no arrival counter, one L2 round trip after the last record lands.  A record is 16 words of 8 bytes, each
+//      {32 data bits, 32-bit exchange number}: an aligned 8-byte access is single-copy atomic, so a word that shows the
+//      right number also shows its data and a reader that is too early simply re-reads.  The poll is warp-wide and
+//      coalesced (8 lanes x 16 bytes = one record, four records per load), which keeps the number of L2 requests per
+//      record line at one per leader and round;
+//   4. cluster: the leader writes the grid's winners into its partner's shared memory and arrives on its mbarrier.
+// With a cluster size of 1 (tiny grids, or a device that cannot co-schedule the clusters) hops 2 and 4 fall away.
 constexpr int REC_WORDS = 16;
 struct __align__(128) Rec { unsigned long long w[REC_WORDS]; };
 
+// word layout: the two 32-bit halves of one value share a 16-byte pair of words
 __device__ __forceinline__ unsigned rec_word(const LocalBest &b, int k)
 {
     switch (k) {
@@ -254,19 +347,19 @@ __device__ __forceinline__ unsigned rec_word(const LocalBest &b, int k)
     default: return (unsigned)((unsigned long long)b.hi.q >> 32);
     }
 }
-__device__ __forceinline__ void rec_unpack(const unsigned long long (&w)[REC_WORDS], LocalBest &b)
+// the 16 data words of a record (as staged in shared memory) -> winners
+__device__ __forceinline__ void rec_unpack32(const unsigned *d, LocalBest &b)
 {
-    auto d = [&](int k) { return (unsigned)(w[k] & 0xffffffffull); };
-    b.lo.f = __hiloint2double((int)d(1), (int)d(0));
-    b.lo.idx = (int)d(2);
-    b.hi.f = __hiloint2double((int)d(4), (int)d(3));
-    b.hi.idx = (int)d(5);
-    b.lo.alpha = __hiloint2double((int)d(7), (int)d(6));
-    b.hi.alpha = __hiloint2double((int)d(9), (int)d(8));
-    b.lo.y = (int)d(10);
-    b.hi.y = (int)d(11);
-    b.lo.q = (long long)(((unsigned long long)d(13) << 32) | d(12));
-    b.hi.q = (long long)(((unsigned long long)d(15) << 32) | d(14));
+    b.lo.f = __hiloint2double((int)d[1], (int)d[0]);
+    b.lo.idx = (int)d[2];
+    b.hi.f = __hiloint2double((int)d[4], (int)d[3]);
+    b.hi.idx = (int)d[5];
+    b.lo.alpha = __hiloint2double((int)d[7], (int)d[6]);
+    b.hi.alpha = __hiloint2double((int)d[9], (int)d[8]);
+    b.lo.y = (int)d[10];
+    b.hi.y = (int)d[11];
+    b.lo.q = (long long)(((unsigned long long)d[13] << 32) | d[12]);
+    b.hi.q = (long long)(((unsigned long long)d[15] << 32) | d[14]);
 }
 template <bool SYS>
 __device__ __forceinline__ void rec_store(Rec *r, const LocalBest &b, unsigned seq)
@@ -279,30 +372,11 @@ __device__ __forceinline__ void rec_store(Rec *r, const LocalBest &b, unsigned s
         else asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
     }
 }
-// read a record; re-read until all 16 words carry `seq`.  Returns false when `budget` polls pass
-// without that (only the multi-GPU mailbox reads pass a finite budget: a peer process may have died).
 template <bool SYS>
-__device__ __forceinline__ bool rec_read(const Rec *r, unsigned seq, LocalBest &out, long long deadline_clock = 0)
+__device__ __forceinline__ void ld_pair(const unsigned long long *p, unsigned long long &w0, unsigned long long &w1)
 {
-    unsigned long long w[REC_WORDS];
-    for (;;) {
-#pragma unroll
-        for (int k = 0; k < REC_WORDS; k += 2) {
-            if (SYS) asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[k]), "=l"(w[k + 1]) : "l"(&r->w[k]) : "memory");
-            else asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[k]), "=l"(w[k + 1]) : "l"(&r->w[k]) : "memory");
-        }
-        bool ok = true;
-#pragma unroll
-        for (int k = 0; k < REC_WORDS; ++k) ok = ok && ((unsigned)(w[k] >> 32) == seq);
-        if (ok) break;
-        if (deadline_clock && clock64() > deadline_clock) return false;
-    }
-    rec_unpack(w, out);
-    return true;
-}
-__device__ __forceinline__ void red_relaxed_gpu_add(unsigned *p, unsigned v)
-{
-    asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    if (SYS) asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+    else asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
 }
 __device__ __forceinline__ unsigned ld_relaxed_gpu_u32(const unsigned *p)
 {
@@ -310,100 +384,246 @@ __device__ __forceinline__ unsigned ld_relaxed_gpu_u32(const unsigned *p)
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ void st_relaxed_gpu_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// ---- thread-block cluster primitives (distributed shared memory + cluster-scope mbarrier operations)
+__device__ __forceinline__ unsigned cluster_ctarank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ unsigned cluster_nctarank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `p` (an address in this CTA's shared memory) in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t dsmem_addr(const void *p, unsigned rank)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(rank));
+    return r;
+}
+// 16 bytes into another CTA's shared memory, completing 16 bytes of the transaction count of ITS mbarrier: data and
+// notification travel together, so the sender needs no fence and the receiver's wait on the barrier publishes the data
+__device__ __forceinline__ void dsmem_st_async2(uint32_t addr, unsigned long long a, unsigned long long b, uint32_t bar_addr)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b64 [%0], {%1, %2}, [%3];"
+                 ::"r"(addr), "l"(a), "l"(b), "r"(bar_addr) : "memory");
+}
+// wait for the phase with the given parity; false when `abort_word` becomes non-zero first (checked now and then)
+__device__ __forceinline__ bool mbar_wait_abortable(uint64_t *bar, unsigned parity, const unsigned *abort_word)
+{
+    unsigned done = 0, spins = 0;
+    for (;;) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (done) return true;
+        if ((++spins & 63u) == 0 && ld_relaxed_gpu_u32(abort_word)) return false;
+    }
+}
+constexpr unsigned BEST_PAIR_BYTES = 64;   // two winners of 32 bytes
+// one side's winner (32 bytes) into CTA-remote shared memory at `addr`, counted on the mbarrier at `bar_addr` there
+__device__ __forceinline__ void dsmem_put_best(uint32_t addr, const Best &b, uint32_t bar_addr)
+{
+    dsmem_st_async2(addr, (unsigned long long)__double_as_longlong(b.f), (unsigned long long)__double_as_longlong(b.alpha), bar_addr);
+    dsmem_st_async2(addr + 16, (unsigned long long)b.q, ((unsigned long long)(unsigned)b.y << 32) | (unsigned)b.idx, bar_addr);
+}
+
+constexpr int SMO_MAX_RECS = 160;         // records per exchange: clusters of the grid (74 on a B200; 148 with a cluster size of 1)
+constexpr int POLL_GROUPS_MAX = 5;        // groups of four records a warp polls: 8 warps x 5 x 4 = 160
+constexpr int REC_STRIDE = REC_WORDS + 1;
 
 struct __align__(16) Shared {
     Best wlo[SMO_MAX_WARPS], whi[SMO_MAX_WARPS];  // per-warp winners of this CTA's rows
-    Best glo[SMO_MAX_WARPS], ghi[SMO_MAX_WARPS];  // per-warp winners over the gathered records
-    Best xlo, xhi;                                // winners over the GPUs' records (row sharding)
-    int xok, xpad_[3];
+    Best plo, phi;                                // cluster leader: the partner CTA's winners (written through DSMEM)
+    Best rlo, rhi;                                // partner CTA: the grid's winners (written through DSMEM by the leader)
+    uint64_t bar_in, bar_out;                     // mbarriers of the two cluster hops
+    unsigned recdata[SMO_MAX_RECS][REC_STRIDE];   // data words of the polled records (odd stride: lane l reads record l without bank conflicts)
 };
 
 #ifdef SVM_TIMING
-#define SVM_STAMP(k) do { if (a.timing && blockIdx.x == 0 && threadIdx.x == 0 && gather_no < a.timing_cap) a.timing[(size_t)gather_no * 16 + (k)] = clock64(); } while (0)
+#define SVM_STAMP_T(k, tid) do { if (a.timing && blockIdx.x == 0 && threadIdx.x == (tid) && gather_no < a.timing_cap) a.timing[(size_t)gather_no * 16 + (k)] = clock64(); } while (0)
+#define SVM_STAMP(k) SVM_STAMP_T(k, 0)
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define SVM_GSTAMP(k) do { if (a.timing && threadIdx.x == 0 && gather_no >= 100 && gather_no < 108) a.timing[(size_t)a.timing_cap * 16 + ((size_t)(gather_no - 100) * gridDim.x + blockIdx.x) * 4 + (k)] = (long long)gtimer(); } while (0)
 #else
+#define SVM_STAMP_T(k, tid) do { } while (0)
 #define SVM_STAMP(k) do { } while (0)
 #define SVM_GSTAMP(k) do { } while (0)
 #endif
 
 constexpr long long PEER_TIMEOUT_CLOCKS = 6000000000LL;   // ~3 s at 1.97 GHz: a peer GPU's process is gone
 
-// One exchange: CTA-level reduce of the per-thread candidates, publish, gather; with row sharding over
-// several GPUs a second level follows in which every GPU stores its record into every peer's mailbox
-// over NVLink (peer-mapped memory, same self-validating words) and reads the others' from its own.
-// On return every thread of every CTA on every GPU holds the same winners in `mine`.  Returns false
-// if a peer never showed up.
+// Poll `count` records starting at `recs` until every word carries `seq`, and stage their data words in shared memory.
+// Called by all warps of a leader CTA; warp w takes the groups of four records w, w + nwarps, ... (8 lanes x 16 bytes
+// cover a record, so a warp's load covers four records in one coalesced request).
+// Returns false if the wait was given up: `abort_word` set by another CTA, or (deadline != 0) the clock ran out, in which
+// case this CTA sets the abort word so that every other wait on this GPU ends too.
+template <bool SYS>
+__device__ __forceinline__ bool poll_records(const Rec *recs, int count, unsigned seq, unsigned (*stage)[REC_STRIDE], unsigned *abort_word,
+                                             long long deadline)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nwarps = (int)(blockDim.x >> 5);
+    const int sub = lane >> 3, pair = lane & 7;
+    unsigned long long w0[POLL_GROUPS_MAX], w1[POLL_GROUPS_MAX];
+    unsigned spins = 0;
+    bool ok_all = true;
+    for (;;) {
+        bool ok = true;
+#pragma unroll
+        for (int u = 0; u < POLL_GROUPS_MAX; ++u) {
+            const int r = (warp + u * nwarps) * 4 + sub;
+            if (r < count) {
+                ld_pair<SYS>(&recs[r].w[2 * pair], w0[u], w1[u]);
+                ok = ok && (unsigned)(w0[u] >> 32) == seq && (unsigned)(w1[u] >> 32) == seq;
+            }
+        }
+        if (__all_sync(FULL, ok)) break;
+        if ((++spins & 255u) == 0) {
+            if (ld_relaxed_gpu_u32(abort_word)) { ok_all = false; break; }
+            if (deadline && clock64() > deadline) { st_relaxed_gpu_u32(abort_word, 1u); ok_all = false; break; }
+        }
+    }
+    if (ok_all) {
+#pragma unroll
+        for (int u = 0; u < POLL_GROUPS_MAX; ++u) {
+            const int r = (warp + u * nwarps) * 4 + sub;
+            if (r < count) { stage[r][2 * pair] = (unsigned)w0[u]; stage[r][2 * pair + 1] = (unsigned)w1[u]; }
+        }
+    }
+    return ok_all;
+}
+// Warp-wide position of the (value, lowest index) winner: the REDUX rounds of best_warp_one on (f, idx), returning the
+// lane that holds it
+template <bool IS_MIN>
+__device__ __forceinline__ int warp_arg_best(double f, int idx)
+{
+    unsigned long long key = order_key(f);
+    if (!IS_MIN) key = ~key;
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mhi = __reduce_min_sync(FULL, hi);
+    const unsigned mlo = __reduce_min_sync(FULL, hi == mhi ? lo : 0xffffffffu);
+    const bool tie = hi == mhi && lo == mlo;
+    const unsigned midx = __reduce_min_sync(FULL, tie ? (unsigned)idx : 0xffffffffu);
+    return __ffs(__ballot_sync(FULL, tie && (unsigned)idx == midx)) - 1;
+}
+// every warp folds the staged records by itself: lane l compares (f, idx) of records l, l + 32, ..., one REDUX round
+// per side finds the winning record, and every lane reads that record's payload
+__device__ __forceinline__ void fold_staged(unsigned (*stage)[REC_STRIDE], int count, LocalBest &g)
+{
+    const int lane = threadIdx.x & 31;
+    double flo = __longlong_as_double(0x7ff0000000000000LL), fhi = __longlong_as_double(0xfff0000000000000LL);
+    int ilo = IDX_NONE, ihi = IDX_NONE, rlo = 0, rhi = 0;
+    for (int r = lane; r < count; r += 32) {
+        const unsigned *d = stage[r];
+        const double f0 = __hiloint2double((int)d[1], (int)d[0]), f1 = __hiloint2double((int)d[4], (int)d[3]);
+        const int i0 = (int)d[2], i1 = (int)d[5];
+        if (better_min(f0, i0, flo, ilo)) { flo = f0; ilo = i0; rlo = r; }
+        if (better_max(f1, i1, fhi, ihi)) { fhi = f1; ihi = i1; rhi = r; }
+    }
+    rlo = __shfl_sync(FULL, rlo, warp_arg_best<true>(flo, ilo));
+    rhi = __shfl_sync(FULL, rhi, warp_arg_best<false>(fhi, ihi));
+    const unsigned *a = stage[rlo], *b = stage[rhi];
+    g.lo.f = __hiloint2double((int)a[1], (int)a[0]);
+    g.lo.idx = (int)a[2];
+    g.lo.alpha = __hiloint2double((int)a[7], (int)a[6]);
+    g.lo.y = (int)a[10];
+    g.lo.q = (long long)(((unsigned long long)a[13] << 32) | a[12]);
+    g.hi.f = __hiloint2double((int)b[4], (int)b[3]);
+    g.hi.idx = (int)b[5];
+    g.hi.alpha = __hiloint2double((int)b[9], (int)b[8]);
+    g.hi.y = (int)b[11];
+    g.hi.q = (long long)(((unsigned long long)b[15] << 32) | b[14]);
+}
+
+// One exchange.  On return every thread of every CTA on every GPU holds the same winners in `mine`.  Returns false
+// if the exchange was abandoned (a peer GPU never showed up): all CTAs of this GPU then return false.
 __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest &mine, int gather_no)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int G = gridDim.x;
     const int nwarps = (int)(blockDim.x >> 5);
+    const unsigned cl = cluster_nctarank(), crank = cluster_ctarank();
+    const int NC = (int)(gridDim.x / cl);                 // records per exchange
+    const int cid = (int)(blockIdx.x / cl);
     const unsigned seq = (unsigned)gather_no + 1u;
+    const unsigned parity = (unsigned)gather_no & 1u;
+    const bool leader = crank == 0;
+    Rec *recs = a.rec + (size_t)(gather_no & 1) * SMO_MAX_RECS;
+
+    // hop 1: this CTA's winners
     best_warp_reduce(mine);
     if (lane == 0) { sh.wlo[warp] = mine.lo; sh.whi[warp] = mine.hi; }
     SVM_STAMP(3);
     __syncthreads();
     SVM_STAMP(4);
-    Rec *recs = a.rec + (size_t)(gather_no & 1) * G;
     if (warp == 0) {
         LocalBest b;
         best_init(b);
         if (lane < nwarps) { b.lo = sh.wlo[lane]; b.hi = sh.whi[lane]; }
-        SVM_STAMP(8);
         best_warp_reduce(b);
-        SVM_STAMP(9);
-        if (lane == 0) {
-            rec_store<false>(recs + blockIdx.x, b, seq);
-            SVM_STAMP(10);
-            red_relaxed_gpu_add(a.arrive, 1u);
+        SVM_STAMP(8);
+        if (!leader) {
+            // hop 2, sender: winners into the leader's shared memory, counted on the leader's mbarrier
+            if (lane == 0) {
+                const uint32_t bar = dsmem_addr(&sh.bar_in, 0);
+                dsmem_put_best(dsmem_addr(&sh.plo, 0), b.lo, bar);
+                dsmem_put_best(dsmem_addr(&sh.phi, 0), b.hi, bar);
+                mbar_expect_tx(&sh.bar_out, BEST_PAIR_BYTES);              // arms this CTA's barrier for hop 4
+            }
+        } else {
+            if (cl > 1) {                                  // hop 2, receiver
+                if (lane == 0) mbar_expect_tx(&sh.bar_in, BEST_PAIR_BYTES);
+                __syncwarp();
+                if (!mbar_wait_abortable(&sh.bar_in, parity, a.abort_word)) b.lo.idx = b.hi.idx = IDX_NONE;
+                best_merge(b, sh.plo, sh.phi);
+            }
             SVM_STAMP(5);
-            const unsigned target = (unsigned)G * seq;
-            while ((int)(ld_relaxed_gpu_u32(a.arrive) - target) < 0) { }
-            __threadfence();      // orders the cached-row reads after the arrivals observed here (pairs with the writers' fence)
+            if (lane == 0) rec_store<false>(recs + cid, b, seq);           // hop 3: publish
             SVM_STAMP(6);
         }
     }
-    __syncthreads();
-    // thread t reads the record of CTA t
-    const int gather_warps = (G + 31) >> 5;
-    if (warp < gather_warps) {
-        LocalBest g;
-        best_init(g);
-        SVM_STAMP(11);
-        if ((int)threadIdx.x < G) rec_read<false>(recs + threadIdx.x, seq, g);
-        SVM_STAMP(12);
-        best_warp_reduce(g);
-        if (lane == 0) { sh.glo[warp] = g.lo; sh.ghi[warp] = g.hi; }
-        SVM_STAMP(13);
-    }
-    __syncthreads();
-    SVM_STAMP(14);
-    best_init(mine);
-    if (lane < gather_warps) { mine.lo = sh.glo[lane]; mine.hi = sh.ghi[lane]; }
-    best_warp_reduce(mine);
-    SVM_STAMP(7);
-    if (a.peers == 1) return true;
-
-    // ---- second level: one record per GPU, all-gathered through the peers' mailboxes
-    const unsigned seq2 = ((unsigned)(a.epoch & 0x7ff) << 21) | seq;
-    const int slot = (gather_no & 1) * a.peers;
-    if (blockIdx.x == 0 && threadIdx.x < a.peers)        // thread p stores this GPU's record at peer p (p == rank: local)
-        rec_store<true>(a.peer_mailbox[threadIdx.x] + slot + a.rank, mine, seq2);
     bool ok = true;
-    if (warp == 0) {
-        LocalBest g;
-        best_init(g);
-        if (lane < a.peers) ok = rec_read<true>(a.mailbox + slot + lane, seq2, g, clock64() + PEER_TIMEOUT_CLOCKS);
-        ok = __all_sync(FULL, ok);
-        best_warp_reduce(g);
-        if (lane == 0) { sh.xlo = g.lo; sh.xhi = g.hi; sh.xok = ok ? 1 : 0; }
+    if (leader) {
+        ok = poll_records<false>(recs, NC, seq, sh.recdata, a.abort_word, 0);
+        SVM_STAMP(11);
+        ok = __syncthreads_and(ok ? 1 : 0) != 0;          // every warp's share is staged
+        SVM_STAMP(12);
+        fold_staged(sh.recdata, NC, mine);
+        SVM_STAMP(13);
+        if (a.peers > 1) {
+            // second level (row sharding): one record per GPU, stored into every peer's mailbox over NVLink (peer-mapped
+            // memory, same self-validating words at system scope) by the first leader, polled locally by every leader.
+            // A peer that never shows up ends the wait after ~3 s; the abort word then ends every other wait on this GPU.
+            const unsigned seq2 = ((unsigned)(a.epoch & 0x7ff) << 21) | seq;
+            const int slot = (gather_no & 1) * 8;
+            if (blockIdx.x == 0 && warp == 0 && lane < a.peers) rec_store<true>(a.peer_mailbox[lane] + slot + a.rank, mine, seq2);
+            __syncthreads();                               // the first level's staged words have been folded by every warp
+            const bool ok2 = poll_records<true>(a.mailbox + slot, a.peers, seq2, sh.recdata, a.abort_word, clock64() + PEER_TIMEOUT_CLOCKS);
+            ok = __syncthreads_and((ok && ok2) ? 1 : 0) != 0;
+            fold_staged(sh.recdata, a.peers, mine);
+        }
+        if (cl > 1 && warp == 0 && lane == 0) {           // hop 4, sender
+            Best lo = mine.lo, hi = mine.hi;
+            if (!ok) lo.y = hi.y = 99;                     // tells the partner that the exchange was abandoned
+            const uint32_t bar = dsmem_addr(&sh.bar_out, 1);
+            dsmem_put_best(dsmem_addr(&sh.rlo, 1), lo, bar);
+            dsmem_put_best(dsmem_addr(&sh.rhi, 1), hi, bar);
+        }
+    } else {
+        // hop 4, receiver: every thread waits for the leader's 64 bytes, then reads the winners
+        ok = mbar_wait_abortable(&sh.bar_out, parity, a.abort_word);
+        mine.lo = sh.rlo;
+        mine.hi = sh.rhi;
+        if (mine.lo.y == 99) ok = false;
+        if (a.peers > 1) ok = __syncthreads_and(ok ? 1 : 0) != 0;
     }
-    __syncthreads();
-    mine.lo = sh.xlo;
-    mine.hi = sh.xhi;
-    ok = sh.xok != 0;
-    return ok;                                            // xlo/xhi/xok are next written two CTA barriers from here
+    SVM_STAMP(7);
+    return ok;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -424,8 +644,14 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     Shared &sh = *reinterpret_cast<Shared *>(bars + WARPS * SMO_KSLOTS_MAX);
     constexpr int RPS = smo_rows_per_step<XT, Q, THREADS>();
     // (RPS == 4) per warp: the two sums of each of the 32 rows of a block, parked until their lane finishes the rows
-    double2 *stage = reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(&sh) + ((sizeof(Shared) + 15) & ~(size_t)15)) + warp * 32;
-
+    double2 *stage_all = reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(&sh) + ((sizeof(Shared) + 15) & ~(size_t)15));
+    double2 *stage = stage_all + warp * 32;
+    // (uint8 rows) per warp: the two integer sums of each of the 32 rows of a block; then the tail weights, shared by the CTA
+    constexpr bool IS_U8 = sizeof(XT) == 1;
+    constexpr int QM = IS_U8 ? Q : 1, QT = IS_U8 ? CH : 1;       // words per lane of the main class / of the tail
+    double *sh_wt = reinterpret_cast<double *>(reinterpret_cast<int2 *>(stage_all + WARPS * 32) + WARPS * 32);
+    if constexpr (IS_U8)
+        for (int k = threadIdx.x; k < a.tw * 4; k += THREADS) sh_wt[k] = a.wt[k];
 
     // rows owned by this CTA and, inside it, by this warp (contiguous ranges)
     const long long n_own = a.row_end - a.row_begin;
@@ -443,9 +669,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     uint64_t *my_bars = bars + warp * SMO_KSLOTS_MAX;
     if (lane == 0) {
         for (int s = 0; s < KS; ++s) mbar_init(&my_bars[s], 1);
+        if (warp == 0) { mbar_init(&sh.bar_in, 1); mbar_init(&sh.bar_out, 1); }
         mbar_fence_init();
     }
     __syncthreads();
+    cluster_sync_all();                  // the partner CTA's mbarriers exist before anything is sent to them
 
     // the ring: rows of this warp's range are requested in order, cyclically, for ever
     // Each slot is refilled right after it is used, so "the slot to use next" is the whole state.
@@ -527,6 +755,59 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         // K12 = K(i_high, i_low)  (main3.cpp:241)
         Pivots<Vec, Q> pv;
         double K12, n_h = 0.0, n_l = 0.0;
+        // uint8 rows: the pivots' main-class words as they are, their tail bytes as weighted doubles w_k * p_k
+        unsigned pm_h[QM], pm_l[QM];
+        double pw_h[QT][4], pw_l[QT][4];
+        int nm_h = 0, nm_l = 0;
+        if constexpr (IS_U8) {
+          if (!use_cache) {
+            const unsigned *xh = reinterpret_cast<const unsigned *>(Xb + (size_t)i_high * row_bytes);
+            const unsigned *xl = reinterpret_cast<const unsigned *>(Xb + (size_t)i_low * row_bytes);
+            unsigned th[QT], tl[QT];
+#pragma unroll
+            for (int i = 0; i < QM; ++i) {
+                const int w = i * 32 + lane;
+                pm_h[i] = w < a.mw ? __ldg(xh + w) : 0u;
+                pm_l[i] = w < a.mw ? __ldg(xl + w) : 0u;
+            }
+#pragma unroll
+            for (int i = 0; i < QT; ++i) {
+                const int w = i * 32 + lane;
+                th[i] = w < a.tw ? __ldg(xh + a.mw + w) : 0u;
+                tl[i] = w < a.tw ? __ldg(xl + a.mw + w) : 0u;
+            }
+            nm_h = a.nmain[i_high]; nm_l = a.nmain[i_low];
+            n_h = a.ntail[i_high]; n_l = a.ntail[i_low];
+            SVM_STAMP(15);
+            int dot = 0;
+#pragma unroll
+            for (int i = 0; i < QM; ++i) dot = __dp4a(pm_l[i], pm_h[i], (unsigned)dot);
+            dot = __reduce_add_sync(FULL, dot);
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i < QT; ++i) {
+                const int w = min(i * 32 + lane, max(a.tw - 1, 0));
+                const bool valid = i * 32 + lane < a.tw;                     // padding words carry zero weights
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const double wk = valid ? sh_wt[4 * w + c] : 0.0;
+                    pw_h[i][c] = wk * u8_to_f64(th[i], c);
+                    pw_l[i][c] = wk * u8_to_f64(tl[i], c);
+                    if (valid) acc = fma(u8_to_f64(tl[i], c), pw_h[i][c], acc);      // row = x_low, pivot = x_high
+                }
+            }
+            acc = warp_sum_butterfly(acc);
+            const int S = nm_l + nm_h - 2 * dot;
+            double tail = (n_l + n_h) - 2.0 * acc;
+            if (tail < 0.0) tail = 0.0;
+            K12 = svm_exp(-a.gamma * fma((double)S, a.wR, tail));
+          } else if (i_low >= a.row_begin && i_low < a.row_end) {
+            __threadfence();
+            K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
+          } else {
+            K12 = u8_kernel_value<QM, QT>(Xb, row_bytes, a.mw, a.tw, sh_wt, a.wR, a.nmain, a.ntail, i_low, i_high, a.gamma, lane);
+          }
+        } else
         if (!use_cache) {
             const Vec *xh = reinterpret_cast<const Vec *>(a.X) + (size_t)i_high * a.pitch4;
             const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)i_low * a.pitch4;
@@ -546,8 +827,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             K12 = svm_exp(-a.gamma * dist2<XT>(n_h, n_l, acc));
         } else if (i_low >= a.row_begin && i_low < a.row_end) {
             // the one read of a value another CTA wrote: column i_low of the cached row was stored by the CTA that
-            // owns row i_low, at least one exchange ago (its __threadfence below, this CTA's fence after the counter
-            // spin).  Read it from L2: this SM's L1 may still hold the line from when the slot cached another row.
+            // owns row i_low, at least one exchange ago (its __threadfence below, this thread's fence here after the
+            // records it observed).  Read it from L2: this SM's L1 may still hold the line from when the slot cached another row.
+            __threadfence();
             K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
         } else {
             // row sharding: column i_low of the cached rows lives on the GPU that owns row i_low; X is
@@ -565,28 +847,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         }
 
         // scalar update, main3.cpp:235-270, operation for operation
-        const int s = lo.y * hi.y;
-        const double K11 = 1.0, K22 = 1.0;                    // exp(-gamma * 0)
-        const double eta = K11 + K22 - 2.0 * K12;
-        const double a_h = lo.alpha, a_l = hi.alpha;
-        double U, V;
-        if (s == -1) {
-            const double u = a_l - a_h, v = a.C + a_l - a_h;
-            U = (0.0 < u) ? u : 0.0;
-            V = (v < a.C) ? v : a.C;
-        } else {
-            const double u = a_l + a_h - a.C, v = a_l + a_h;
-            U = (0.0 < u) ? u : 0.0;
-            V = (v < a.C) ? v : a.C;
-        }
-        if (!(U <= V + 1e-12)) { stop = 2; break; }            // main3.cpp:246
-        if (eta <= a.eps) { stop = 3; break; }                  // main3.cpp:253
-        double na_l = a_l + hi.y * (b_high - b_low) / eta;      // main3.cpp:259
-        if (na_l > V) na_l = V;
-        if (na_l < U) na_l = U;
-        const double na_h = a_h + s * (a_l - na_l);             // main3.cpp:266
-        const double c_h = (na_h - a_h) * lo.y;                 // delta_alpha_i_high * y[i_high]
-        const double c_l = (na_l - a_l) * hi.y;
+        const PairStep ps = pair_update(lo.y, hi.y, lo.alpha, hi.alpha, b_high, b_low, K12, a.C, a.eps);
+        if (ps.stop) { stop = ps.stop; break; }                 // main3.cpp:246 / :253
+        const double na_h = ps.na_h, na_l = ps.na_l, c_h = ps.c_h, c_l = ps.c_l;
 
         if (blockIdx.x == 0 && threadIdx.x == 0 && a.rank == 0 && num_iter - 1 < a.trace_cap) {
             a.trace[2 * (num_iter - 1)] = (int)i_high;
@@ -611,7 +874,152 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         if (!use_cache) {
             // ---------------- X pass: a warp per group of RPS rows (or per row, below) ----------------
             ++x_passes;
-            if constexpr (RPS > 1) {
+            if constexpr (IS_U8) {
+              // ---------------- uint8 rows: a warp per group of eight rows ----------------
+              // both sections of a row are padded with zero bytes to whole 128-byte slots (32 lanes x one word), so a lane's
+              // words sit at constant offsets from one address per row and need no bounds test
+              const int qm = a.mw >> 5, qt = a.tw >> 5;                        // slots really in use (warp-uniform)
+              const int tail_off = a.mw * 4;
+              for (int base = 0; base < m; base += 32) {
+                const int cnt = min(32, m - base);
+                const long long j = w0 + base + lane;
+                double fj = 0.0, aj = 0.0, ntj = 0.0;
+                int yj = 0, nmj = 0;
+                long long qj = -1;
+                if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; nmj = a.nmain[j]; ntj = a.ntail[j]; if (a.cacheq) qj = a.cacheq[j]; }
+                int my_sh = 0, my_sl = 0;                  // the integer dot products of this lane's row of the block
+                for (int t = 0; t < cnt; t += RPS) {
+                    const int rows_here = min(RPS, cnt - t);
+                    mbar_wait(&my_bars[cslot], cphase);
+                    const unsigned char *grp = my_slots + (size_t)cslot * RPS * row_bytes;
+                    int SI[2 * RPS];                       // [pivot * RPS + row] integer dot products over the main class
+                    double P[2 * RPS];                     // the same for the weighted tail
+#pragma unroll
+                    for (int k = 0; k < 2 * RPS; ++k) { SI[k] = 0; P[k] = 0.0; }
+                    const unsigned char *lanep = grp + lane * 4;
+                    if (rows_here == RPS) {
+                        // a full group: word slot by word slot, the eight rows side by side (sixteen independent sums)
+#pragma unroll
+                        for (int i = 0; i < QM; ++i)
+                            if (i < qm) {
+                                unsigned w[RPS];
+#pragma unroll
+                                for (int r = 0; r < RPS; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + r * row_bytes + i * 128);
+#pragma unroll
+                                for (int r = 0; r < RPS; ++r) {
+                                    SI[r] = (int)__dp4a(w[r], pm_h[i], (unsigned)SI[r]);
+                                    SI[RPS + r] = (int)__dp4a(w[r], pm_l[i], (unsigned)SI[RPS + r]);
+                                }
+                            }
+#pragma unroll
+                        for (int i = 0; i < QT; ++i)
+                            if (i < qt) {
+                                unsigned w[RPS];
+#pragma unroll
+                                for (int r = 0; r < RPS; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + tail_off + r * row_bytes + i * 128);
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                                    for (int r = 0; r < RPS; ++r) {
+                                        const double ud = u8_to_f64(w[r], c);
+                                        P[r] = fma(ud, pw_h[i][c], P[r]);
+                                        P[RPS + r] = fma(ud, pw_l[i][c], P[RPS + r]);
+                                    }
+                                }
+                            }
+                    } else {
+                        // the short group at the end of a CTA's rows
+                        for (int r = 0; r < rows_here; ++r) {
+                            const unsigned char *rowp = lanep + (size_t)r * row_bytes;
+                            int sh_ = 0, sl_ = 0;
+                            double th_ = 0.0, tl_ = 0.0;
+#pragma unroll
+                            for (int i = 0; i < QM; ++i)
+                                if (i < qm) {
+                                    const unsigned w = *reinterpret_cast<const unsigned *>(rowp + i * 128);
+                                    sh_ = (int)__dp4a(w, pm_h[i], (unsigned)sh_);
+                                    sl_ = (int)__dp4a(w, pm_l[i], (unsigned)sl_);
+                                }
+#pragma unroll
+                            for (int i = 0; i < QT; ++i)
+                                if (i < qt) {
+                                    const unsigned w = *reinterpret_cast<const unsigned *>(rowp + tail_off + i * 128);
+#pragma unroll
+                                    for (int c = 0; c < 4; ++c) {
+                                        const double ud = u8_to_f64(w, c);
+                                        th_ = fma(ud, pw_h[i][c], th_);
+                                        tl_ = fma(ud, pw_l[i][c], tl_);
+                                    }
+                                }
+                            // P[] / SI[] are indexed with constants only (they live in registers)
+#pragma unroll
+                            for (int k = 0; k < RPS; ++k)
+                                if (k == r) { SI[k] = sh_; SI[RPS + k] = sl_; P[k] = th_; P[RPS + k] = tl_; }
+                        }
+                    }
+                    __syncwarp();
+                    fence_proxy_async();
+                    issue_into(cslot);
+                    if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
+                    // halving exchanges over the 16 sums (integers and doubles alike): offset 16 splits by pivot, 8 / 4 / 2 by row,
+                    // offset 1 adds; a lane ends with the warp sum for pivot lane >> 4 and row (lane >> 1) & 7.  The doubles are
+                    // added in xor-butterfly order (same bits in every lane of the plain butterfly).
+                    double v1;
+                    {
+                        double v8[8], v4[4], v2[2];
+                        {
+                            const bool up = (lane & 16) != 0;
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) v8[k] = (up ? P[8 + k] : P[k]) + __shfl_xor_sync(FULL, up ? P[k] : P[8 + k], 16);
+                        }
+                        {
+                            const bool up = (lane & 8) != 0;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) v4[k] = (up ? v8[4 + k] : v8[k]) + __shfl_xor_sync(FULL, up ? v8[k] : v8[4 + k], 8);
+                        }
+                        {
+                            const bool up = (lane & 4) != 0;
+#pragma unroll
+                            for (int k = 0; k < 2; ++k) v2[k] = (up ? v4[2 + k] : v4[k]) + __shfl_xor_sync(FULL, up ? v4[k] : v4[2 + k], 4);
+                        }
+                        {
+                            const bool up = (lane & 2) != 0;
+                            v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 2);
+                        }
+                        v1 = v1 + __shfl_xor_sync(FULL, v1, 1);
+                    }
+                    {
+                        const int r = (lane >> 1) & 7;
+                        if (!(lane & 1) && r < rows_here) *(reinterpret_cast<double *>(&stage[t + r]) + (lane >> 4)) = v1;
+                    }
+                    // the integer sums are exact in any order: the hardware warp reduction, the row's own lane keeps the result
+#pragma unroll
+                    for (int r = 0; r < RPS; ++r) {
+                        const int sh_ = __reduce_add_sync(FULL, SI[r]), sl_ = __reduce_add_sync(FULL, SI[RPS + r]);
+                        if (lane == t + r) { my_sh = sh_; my_sl = sl_; }
+                    }
+                }
+                __syncwarp();
+                if (lane < cnt) {
+                    const double2 dd = stage[lane];
+                    const int2 ii = make_int2(my_sh, my_sl);
+                    double t_h = (ntj + n_h) - 2.0 * dd.x, t_l = (ntj + n_l) - 2.0 * dd.y;
+                    if (t_h < 0.0) t_h = 0.0;
+                    if (t_l < 0.0) t_l = 0.0;
+                    const double kh = svm_exp(-a.gamma * fma((double)(nmj + nm_h - 2 * ii.x), a.wR, t_h));
+                    const double kl = svm_exp(-a.gamma * fma((double)(nmj + nm_l - 2 * ii.y), a.wR, t_l));
+                    fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
+                    a.f[j] = fj;
+                    if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
+                    if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
+                    if (slot_h >= 0 && !(hit_h && hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
+                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
+                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
+                    best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                }
+                __syncwarp();                                  // the parked sums have been read: the next block may overwrite them
+              }
+            } else if constexpr (RPS > 1) {
               constexpr bool NEUTRAL_PAD = sizeof(XT) == 4;   // fp32 rows form dot products: an element times a zero pivot register adds +-0.
                                                               // FP64 rows form squared differences: elements beyond the row must be skipped
               const int ng = (a.pitch4 + 31) >> 5;                                 // register groups the row really has (<= Q)
@@ -799,6 +1207,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             mbar_wait(&my_bars[cslot], cphase);
             if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
         }
+    cluster_sync_all();                  // no CTA leaves while its partner may still write into its shared memory
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         SmoResult r;
         r.num_iter = num_iter; r.stop_reason = stop;
@@ -809,11 +1218,29 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     }
 }
 
+// ---- row sharding: the GPUs meet before the timed launch.  Thread p stores this launch's number into GPU p's flag
+// [rank] (peer-mapped memory) and waits until GPU p's number shows in its own flag [p]; gives up after ~3 s (the SMO
+// kernel that follows then ends with PEER_LOST by itself).
+struct PeerFlags { unsigned long long *peer[8]; };
+__global__ void peer_rendezvous_kernel(PeerFlags pf, int rank, int peers, unsigned long long epoch)
+{
+    const int p = threadIdx.x;
+    if (p >= peers || !pf.peer[p]) return;
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(pf.peer[p] + rank), "l"(epoch) : "memory");
+    const long long deadline = clock64() + PEER_TIMEOUT_CLOCKS;
+    for (;;) {
+        unsigned long long v;
+        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(pf.peer[rank] + p) : "memory");
+        if (v >= epoch || clock64() > deadline) break;
+    }
+}
+
 // kslots: ring depth per warp in slots; a slot holds rows_per_step rows
-inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1)
+inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1, int tail_words = 0)
 {
     return (size_t)warps * kslots * rows_per_step * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128 +
-           (size_t)warps * 32 * sizeof(double2);                 // + the parked sums of the four-rows-per-step pass
+           (size_t)warps * 32 * (sizeof(double2) + sizeof(int2)) +   // + the parked sums of the rows-in-groups passes
+           (size_t)tail_words * 4 * sizeof(double);                  // + the tail weights (uint8 rows)
 }
 
 } // namespace svm

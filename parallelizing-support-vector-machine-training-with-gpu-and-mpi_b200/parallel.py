@@ -42,7 +42,14 @@ class ShardedSolver:
         """All ranks call this in lockstep with the same parameters.  Returns the stats of this rank with
         the FULL alpha (all-gathered) and installs the model for sv_ids / predict."""
         n = self.s.n
+        # the ranks meet here first: first-call module loads, a large cache allocation or a slow upload on one rank must not
+        # eat into the ~3 s the kernels wait for a peer's record
+        if dist.get_backend() == "nccl":
+            torch.cuda.synchronize()
+        dist.barrier()
         out = self.s.smo_train(**params)
+        if out.get("stop_reason") == 5:
+            raise RuntimeError(f"rank {self.rank}: a peer GPU's record never arrived (PEER_LOST); no model was produced")
         r0, r1 = self.row_range(n)
         chunk = (n + self.world - 1) // self.world + 1
         mine = torch.zeros(chunk, dtype=torch.float64)
