@@ -109,8 +109,8 @@ int svmb200_set_train_f64(svmb200_ctx *ctx, const double  *X, const int32_t *y, 
  * ten digits is ten label vectors on the same X).  The kernel-row cache survives (see svmb200_params.keep_cache). */
 int svmb200_set_labels(svmb200_ctx *ctx, const int32_t *y);
 
-/* Storage precision of X for the NEXT svmb200_set_train_* call: 0 (default) = fp32 rows, the fast path the
- * roofline numbers are quoted on; 1 = FP64 rows ("exact"): twice the bytes per iteration, K formed from FP64 squared
+/* Storage precision of X for the NEXT svmb200_set_train_* call: 0 = the default (SVMB200_STORAGE_AUTO, below);
+ * 1 = FP64 rows ("exact"): twice the bytes of fp32 rows per iteration, K formed from FP64 squared
  * differences as in main3.cpp:97-100, so that the selected (i_high, i_low) sequence is the reference's own
  * (DESIGN.md "Numerics").  Exact storage takes d <= 832. */
 int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable);
@@ -121,7 +121,10 @@ int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable);
  * (main3.cpp:74-89, :97-100) is (u_k - p_k)^2 / range_k^2: the features that share the most frequent range are summed as exact
  * integers (four products per IDP4A), the rest in FP64 with their weights (DESIGN.md "Numerics").  K agrees with the reference's
  * to ~1e-16 and the solver walks the reference's own (i_high, i_low) sequence, like FP64 storage, at a fraction of the bytes.
- * The decision function (svmb200_predict_*, warm start) then works on scaled FP64 rows.  d <= 832. */
+ * The decision function (svmb200_predict_*, warm start) then works on scaled FP64 rows.  d <= 832.
+ * SVMB200_STORAGE_AUTO, the default of a new context: uint8 storage for svmb200_set_train_u8 with d <= 832, fp32 rows for
+ * every other upload. */
+#define SVMB200_STORAGE_AUTO (-1)
 #define SVMB200_STORAGE_F32 0
 #define SVMB200_STORAGE_F64 1
 #define SVMB200_STORAGE_U8  2

@@ -151,10 +151,11 @@ class Solver:
         """FP64 storage of X for the next set_train_* (the exact path); False = fp32 (default)."""
         self._ck(self.L.svmb200_set_exact(self.h, 1 if enable else 0), "set_exact")
 
-    STORAGE = {"f32": 0, "f64": 1, "u8": 2}
+    STORAGE = {"auto": -1, "f32": 0, "f64": 1, "u8": 2}
 
     def set_storage(self, storage: str):
-        """How the next set_train_* keeps X: "f32" (default), "f64" (exact), "u8" (set_train_u8 only: the bytes themselves)."""
+        """How the next set_train_* keeps X: "auto" (default: bytes stay bytes, everything else fp32), "f32", "f64" (exact),
+        "u8" (set_train_u8 only: the bytes themselves)."""
         self._ck(self.L.svmb200_set_storage(self.h, self.STORAGE[storage]), "set_storage")
 
     def u8_layout(self):

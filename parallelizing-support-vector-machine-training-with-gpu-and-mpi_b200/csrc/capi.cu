@@ -45,7 +45,8 @@ struct svmb200_ctx {
     long long n = 0;
     int d = 0, pitch4 = 0;
     void *X = nullptr;          // fp32 rows, FP64 rows when x_f64, packed uint8 rows when x_u8
-    int storage_requested = SVMB200_STORAGE_F32;   // for the next svmb200_set_train_*
+    int storage_requested = SVMB200_STORAGE_AUTO;  // for the next svmb200_set_train_*
+    int storage_resolved = SVMB200_STORAGE_F32;    // what AUTO became for the upload in progress
     bool x_f64 = false, x_u8 = false;
     // the rows the decision function works on (support-vector block, query rows): fp32 with fp32 storage, FP64 otherwise
     bool dec_f64 = false;
@@ -260,7 +261,7 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
 {
     if (n <= 0 || d <= 0) FAIL(SVMB200_EINVAL, "n and d must be positive (n=%lld d=%d)", n, d);
     if (n >= 0x7fffffffLL) FAIL(SVMB200_ELIMIT, "n=%lld exceeds the 2^31-2 row limit", n);
-    const bool f64 = ctx->storage_requested == SVMB200_STORAGE_F64, u8 = ctx->storage_requested == SVMB200_STORAGE_U8;
+    const bool f64 = ctx->storage_resolved == SVMB200_STORAGE_F64, u8 = ctx->storage_resolved == SVMB200_STORAGE_U8;
     const bool dec_f64 = f64 || u8;
     const int dec_pitch4 = dec_f64 ? (d + 1) / 2 : (d + 3) / 4;  // 16-byte groups per row of the decision function's rows
     if (dec_pitch4 > max_pitch(dec_f64))
@@ -421,8 +422,12 @@ static int set_train(svmb200_ctx *ctx, const T *X, const int32_t *y, int64_t n, 
 {
     if (!ctx) return SVMB200_EINVAL;
     if (!X || !y) FAIL(SVMB200_EINVAL, "X and y must not be NULL");
-    const bool u8 = ctx->storage_requested == SVMB200_STORAGE_U8;
-    if (u8 && !(std::is_same<T, uint8_t>::value && scale))
+    // AUTO: bytes stay bytes (svmb200_set_train_u8 with up to 832 features), everything else becomes fp32 rows
+    const bool bytes_in = std::is_same<T, uint8_t>::value && scale;
+    ctx->storage_resolved = ctx->storage_requested != SVMB200_STORAGE_AUTO ? ctx->storage_requested
+                            : (bytes_in && d <= 832) ? SVMB200_STORAGE_U8 : SVMB200_STORAGE_F32;
+    const bool u8 = ctx->storage_resolved == SVMB200_STORAGE_U8;
+    if (u8 && !bytes_in)
         FAIL(SVMB200_ESTATE, "uint8 storage keeps the bytes of svmb200_set_train_u8: choose fp32 or FP64 storage for FP64 input");
     if (int rc = alloc_train(ctx, n, d)) return rc;
     if (int rc = ingest<T>(ctx, X, n, scale, scale, u8 ? nullptr : ctx->X, ctx->x_f64, ctx->pitch4)) return rc;
@@ -476,7 +481,7 @@ extern "C" int svmb200_set_labels(svmb200_ctx *ctx, const int32_t *y)
 extern "C" int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable)
 {
     if (!ctx) return SVMB200_EINVAL;
-    ctx->storage_requested = enable ? SVMB200_STORAGE_F64 : SVMB200_STORAGE_F32;
+    ctx->storage_requested = enable ? SVMB200_STORAGE_F64 : SVMB200_STORAGE_AUTO;
     return SVMB200_OK;
 }
 
@@ -484,8 +489,8 @@ extern "C" int svmb200_set_exact(svmb200_ctx *ctx, int32_t enable)
 extern "C" int svmb200_set_storage(svmb200_ctx *ctx, int32_t storage)
 {
     if (!ctx) return SVMB200_EINVAL;
-    if (storage != SVMB200_STORAGE_F32 && storage != SVMB200_STORAGE_F64 && storage != SVMB200_STORAGE_U8)
-        FAIL(SVMB200_EINVAL, "storage must be SVMB200_STORAGE_F32, _F64 or _U8");
+    if (storage != SVMB200_STORAGE_AUTO && storage != SVMB200_STORAGE_F32 && storage != SVMB200_STORAGE_F64 && storage != SVMB200_STORAGE_U8)
+        FAIL(SVMB200_EINVAL, "storage must be SVMB200_STORAGE_AUTO, _F32, _F64 or _U8");
     ctx->storage_requested = storage;
     return SVMB200_OK;
 }

@@ -28,8 +28,10 @@ def O():
 
 @pytest.fixture(scope="session")
 def solver(pkg):
-    """One context on cuda:0 shared by the GPU tests (fails loudly without the built library)."""
+    """One context on cuda:0 shared by the GPU tests (fails loudly without the built library).  fp32 rows: these tests
+    check the fp32 arithmetic; the default storage of uint8 input (the bytes themselves) has tests/test_gpu_u8.py."""
     s = pkg.Solver(0)
+    s.set_storage("f32")
     yield s
     s.close()
 

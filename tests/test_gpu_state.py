@@ -23,6 +23,7 @@ def test_context_reuse_from_narrow_to_wide_rows_and_to_exact_storage(pkg, O):
     """Every row becomes a support vector (random labels, large C), so the SV block of the second problem is far
     larger, in bytes, than what the first one allocated."""
     s = pkg.Solver(0)
+    s.set_storage("f32")
     try:
         Xa, ya = _blobs(64, 16, 1)
         s.set_train_u8(Xa, ya)
@@ -39,7 +40,7 @@ def test_context_reuse_from_narrow_to_wide_rows_and_to_exact_storage(pkg, O):
         c, scores = s.predict_u8(Xb[:200], yb[:200])
         assert c == ref_c and np.array_equal(scores, ref_scores)
         # the same context switched to FP64 rows: the pitch doubles
-        s.set_exact(True)
+        s.set_storage("f64")
         s.set_train_u8(Xb, yb)
         out = s.smo_train(C=1000.0, gamma=0.01)
         ref_c, ref_scores = O.predict(xs[:200], yb[:200], xs, yb, out["alpha"], out["b"], gamma=0.01, arith=O.ARITH_DEVICE_F64)
@@ -135,6 +136,7 @@ def test_infeasible_box_stops_the_solver(pkg, O):
     a0[0] = 25.0          # y = +1, alpha > C: f_0 = 24 is the maximum over I_low; i_high is a y = +1 row with alpha = 0,
                           # so s = +1, U = max(0, 25 + 0 - C) = 15 > V = min(C, 25) = 10
     s = pkg.Solver(0)
+    s.set_storage("f32")
     try:
         s.set_train_u8(X, y)
         out = s.smo_train(alpha0=a0, gamma=10.0)
