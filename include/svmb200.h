@@ -189,6 +189,43 @@ int svmb200_shard_setup(svmb200_ctx *ctx, int32_t rank, int32_t world, void *han
 int svmb200_shard_connect(svmb200_ctx *ctx, int32_t world, const void *handles /* world x 64 bytes */);
 int svmb200_set_model(svmb200_ctx *ctx, const double *alpha, double b);
 
+/* ---- Cascade SVM over the GPUs of one box (BASELINE.json configs[4]): replaces the round loops of the reference's MPI
+ * programs, the modified two-layer ("star") cascade code/mpi_svm_main2.cpp:439-769 and the classical binary-tree cascade
+ * code/mpi_svm_main3.cpp:565-828.  One rank per GPU (a process or a thread each with its own context); the support-vector
+ * tuples the reference ships as blocking host messages (mpi_svm_main2.cpp:445-458,578-607,751-757; mpi_svm_main3.cpp:587-601,
+ * 689-716) travel GPU to GPU with NCCL: ncclAllGather (star gather), ncclSend / ncclRecv (tree levels), ncclBroadcast (feedback
+ * of the global set).  A rank's partition is uploaded once as the uint8 bytes it arrives as and stays on the device; every
+ * stage's training set is assembled, packed and solved there (svmb200_smo_train with warm start, mpi_svm_main2.cpp:167-183);
+ * only ids, labels and alphas are looked at on the host.  NCCL is bound at run time (libnccl.so.2).
+ *   svmb200_cascade_unique_id   on one rank: 128 bytes to hand to every rank (MPI_Bcast, torch.distributed, a pipe ...)
+ *   svmb200_cascade_connect     on every rank: joins the communicator (ncclCommInitRank)
+ *   svmb200_cascade_set_partition_u8  this rank's rows [n_part x d] with global ids first_id .. first_id + n_part - 1
+ *                               (contiguous chunks of ceil(n / P) rows, mpi_svm_main2.cpp:346-402) and labels; computes the
+ *                               global min / max over all ranks' rows (the reference: rank 0 over all data, :404-419)
+ *   svmb200_cascade_train       all ranks together: rounds until the support-vector id set repeats (:646-660) or max_rounds
+ *                               (the reference's 50, :428); afterwards EVERY rank's context holds the final model:
+ *                               svmb200_predict_u8 (ge_zero = 1 is the MPI programs' rule, :729), svmb200_cascade_get_model
+ *   svmb200_cascade_get_model   global ids and alphas of the final support vectors
+ * The tree needs a power-of-two number of ranks (mpi_svm_main3.cpp:420-428).  d <= 832. */
+#define SVMB200_CASCADE_STAR 0
+#define SVMB200_CASCADE_TREE 1
+typedef struct {
+    int32_t rounds;          /* rounds run (the reference prints "Cascade finished in N rounds") */
+    int32_t converged;       /* 1: the id set repeated */
+    int32_t n_sv;
+    double  b;
+    double  train_ms;        /* wall time of the call */
+    int64_t smo_iterations;  /* SMO iterations of this rank's stages */
+    int32_t stages;          /* SMO_train calls of this rank */
+} svmb200_cascade_stats;
+int svmb200_cascade_unique_id(void *id128);
+int svmb200_cascade_connect(svmb200_ctx *ctx, int32_t rank, int32_t world, const void *id128);
+int svmb200_cascade_set_partition_u8(svmb200_ctx *ctx, const uint8_t *X_part, const int32_t *y_part, int64_t n_part, int32_t d,
+                                     int64_t first_id, int64_t n_total);
+int svmb200_cascade_train(svmb200_ctx *ctx, int32_t mode, const svmb200_params *params, int32_t max_rounds,
+                          svmb200_cascade_stats *stats);
+int svmb200_cascade_get_model(svmb200_ctx *ctx, int32_t *ids, double *alpha, int32_t cap, int32_t *count);
+
 /* ---- the decision function on the tensor cores (tcgen05 / TMEM, TF32x3): svmb200_predict_* on fp32 storage first
  * forms all scores with the tensor cores (error up to ~1e-3: fp32 accumulation of three tf32 products), then
  * re-evaluates every row with |score| < recheck_threshold by the exact kernel, so predicted labels and accuracy are

@@ -36,6 +36,11 @@ class Stats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class CascadeStats(C.Structure):
+    _fields_ = [("rounds", C.c_int32), ("converged", C.c_int32), ("n_sv", C.c_int32), ("b", C.c_double), ("train_ms", C.c_double),
+                ("smo_iterations", C.c_int64), ("stages", C.c_int32)]
+
+
 def declared_symbols() -> list[str]:
     """Every function include/svmb200.h declares (used by the export test)."""
     text = open(HEADER).read()
@@ -97,6 +102,11 @@ def load_library():
     L.svmb200_shard_connect.argtypes = [vp, i32, vp]
     L.svmb200_set_model.argtypes = [vp, vp, dbl]
     L.svmb200_minmax_u8_noalloc.argtypes = [C.c_int, vp, i64, i32, vp, vp, vp]
+    L.svmb200_cascade_unique_id.argtypes = [vp]
+    L.svmb200_cascade_connect.argtypes = [vp, i32, i32, vp]
+    L.svmb200_cascade_set_partition_u8.argtypes = [vp, vp, vp, i64, i32, i64, i64]
+    L.svmb200_cascade_train.argtypes = [vp, i32, C.POINTER(Params), i32, C.POINTER(CascadeStats)]
+    L.svmb200_cascade_get_model.argtypes = [vp, vp, vp, i32, C.POINTER(i32)]
     _lib = L
     return L
 
@@ -109,6 +119,16 @@ def default_params(**kw) -> Params:
             raise TypeError(f"unknown parameter {k}")
         setattr(p, k, v)
     return p
+
+
+def cascade_unique_id() -> bytes:
+    """128 bytes that every rank of a cascade passes to Solver.cascade_connect (made on one rank, handed to the others)."""
+    L = load_library()
+    buf = C.create_string_buffer(128)
+    rc = L.svmb200_cascade_unique_id(buf)
+    if rc != 0:
+        raise SvmB200Error(f"svmb200_cascade_unique_id = {rc}: {L.svmb200_last_error(None).decode()}")
+    return buf.raw
 
 
 def _ptr(a):
@@ -275,6 +295,36 @@ class Solver:
     def set_model(self, alpha, b):
         alpha = np.ascontiguousarray(alpha, dtype=np.float64)
         self._ck(self.L.svmb200_set_model(self.h, _ptr(alpha), float(b)), "set_model")
+
+    # ---- Cascade SVM over several GPUs (one rank per GPU)
+    MODES = {"star": 0, "tree": 1}
+
+    def cascade_connect(self, rank: int, world: int, unique_id: bytes):
+        assert len(unique_id) == 128
+        self._ck(self.L.svmb200_cascade_connect(self.h, rank, world, C.c_char_p(unique_id)), "cascade_connect")
+
+    def cascade_set_partition_u8(self, X_part, y_part, first_id: int, n_total: int):
+        X_part = np.ascontiguousarray(X_part, dtype=np.uint8)
+        y_part = np.ascontiguousarray(y_part, dtype=np.int32)
+        n, d = X_part.shape
+        self._ck(self.L.svmb200_cascade_set_partition_u8(self.h, _ptr(X_part), _ptr(y_part), n, d, first_id, n_total), "cascade_set_partition_u8")
+        self.d = d
+
+    def cascade_train(self, mode: str = "star", max_rounds: int = 50, params: Params | None = None, **kw):
+        p = params or default_params(**kw)
+        st = CascadeStats()
+        self._ck(self.L.svmb200_cascade_train(self.h, self.MODES[mode], C.byref(p), max_rounds, C.byref(st)), "cascade_train")
+        out = {k: getattr(st, k) for k, _ in st._fields_}
+        self.n = out["n_sv"]
+        return out
+
+    def cascade_get_model(self):
+        c = C.c_int32()
+        self._ck(self.L.svmb200_cascade_get_model(self.h, None, None, 0, C.byref(c)), "cascade_get_model")
+        ids = np.zeros(max(c.value, 1), dtype=np.int32)
+        alpha = np.zeros(max(c.value, 1))
+        self._ck(self.L.svmb200_cascade_get_model(self.h, _ptr(ids), _ptr(alpha), c.value, C.byref(c)), "cascade_get_model")
+        return ids[:c.value], alpha[:c.value]
 
     # ---- introspection
     def get_trace(self, cap):

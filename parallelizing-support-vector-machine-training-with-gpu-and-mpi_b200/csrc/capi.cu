@@ -5,6 +5,7 @@
 #include "../../include/svmb200.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -32,6 +33,10 @@ extern "C" int svmb200_debug_timing_grid(long long *out)
     return cudaMemcpy(out, g_timing_dev + 4096 * 16, (size_t)8 * 160 * 4 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
 }
 #endif
+
+struct svmb200_cascade_state;
+struct svmb200_ctx;
+static void cascade_destroy(svmb200_ctx *ctx);
 
 struct svmb200_ctx {
     int device = 0;
@@ -118,6 +123,7 @@ struct svmb200_ctx {
     size_t svP_bytes = 0;
     bool svP_valid = false;
     int launches = 0;
+    svmb200_cascade_state *cascade = nullptr;     // Cascade SVM over several GPUs (cascade.cuh)
 };
 
 #define CK(call)                                                                                        \
@@ -238,6 +244,7 @@ void svmb200_destroy(svmb200_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    cascade_destroy(ctx);
     cudaFree(ctx->X); cudaFree(ctx->y); cudaFree(ctx->sqn); cudaFree(ctx->svn); cudaFree(ctx->minv); cudaFree(ctx->maxv);
     cudaFree(ctx->f); cudaFree(ctx->alpha); cudaFree(ctx->cacheq); cudaFree(ctx->cacheK);
     cudaFree(ctx->rec); cudaFree(ctx->result); cudaFree(ctx->trace);
@@ -1555,3 +1562,5 @@ int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs)
 }
 
 } // extern "C"
+
+#include "cascade.cuh"
