@@ -56,8 +56,13 @@ typedef struct {
     double  tau;
     int32_t max_iter;
     double  sv_tol;
-    int32_t wss;          /* working-set selection: 1 = first-order maximal violating pair, the only
-                             rule the reference has (main3.cpp:107-142).  Other values: EINVAL. */
+    int32_t wss;          /* working-set selection.  1 = first-order maximal violating pair, the only rule the reference has
+                             (main3.cpp:107-142).  2 = second-order choice of i_low (Fan, Chen, Lin 2005, the rule of LIBSVM; NOT
+                             in the reference, parity unpinned): i_high and the stop test as in 1, i_low = the row of I_low with
+                             f_t > b_high that maximises (f_t - b_high)^2 / (2 - 2 K(i_high, t)), lowest index on ties, rows with
+                             a curvature <= eps passed over; needs K(i_high, .) before i_low is known, i.e. one more pass (or
+                             row-cache read) and one more exchange per iteration, for about a third fewer iterations.
+                             Other values: EINVAL. */
     int32_t warm_start;   /* 0: alpha := 0, f := -y (main3.cpp:167-172).  1: alpha is in/out and f is
                              rebuilt from it (mpi_svm_main2.cpp:167-183, "init = false"). */
     int32_t cache_rows;   /* HBM kernel-row cache capacity in rows; 0 = off (the reference's behaviour:

@@ -19,7 +19,7 @@ STOP_NAMES = {0: "converged", 1: "not_found", 2: "infeasible_uv", 3: "nonpositiv
 
 class Params(C.Structure):
     _fields_ = [("C", C.c_double), ("gamma", C.c_double), ("eps", C.c_double), ("tau", C.c_double),
-                ("max_iter", C.c_int), ("sv_tol", C.c_double)]
+                ("max_iter", C.c_int), ("sv_tol", C.c_double), ("wss", C.c_int)]
 
 
 class Result(C.Structure):

@@ -20,6 +20,7 @@ void oracle_default_params(oracle_params *p)
     p->tau = 1e-5;        /* code/main3.cpp:196     */
     p->max_iter = 100000; /* code/main3.cpp:198     */
     p->sv_tol = 1e-8;     /* code/main3.cpp:367     */
+    p->wss = 1;           /* the reference's only rule, code/main3.cpp:107-142 */
 }
 
 /* code/main3.cpp:92-104 */
@@ -440,6 +441,21 @@ int oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
             i_high_prev = i_high;
             kernel_row(x, x32, sqn, n, d, i_high, gamma, arith, K_h);
             ++rows;
+        }
+        if (p->wss == 2) {
+            /* second-order choice of i_low (not in the reference; see smo_oracle.h) */
+            size_t best = n;
+            double best_gain = -INFINITY;
+            for (size_t t = 0; t < n; ++t) {
+                int in_low = (y[t] == 1 && alpha[t] > 0.0 + eps) || (y[t] == -1 && alpha[t] < C - eps);
+                if (!in_low || !(f[t] > b_high)) continue;
+                double eta_t = 1.0 + 1.0 - 2.0 * K_h[t];
+                if (eta_t <= eps) continue;
+                double diff = f[t] - b_high;
+                double gain = diff * diff / eta_t;
+                if (gain > best_gain) { best_gain = gain; best = t; }
+            }
+            if (best < n) { i_low = best; b_low = f[i_low]; }
         }
         if (i_low != i_low_prev) { /* :225-232 */
             i_low_prev = i_low;

@@ -31,6 +31,9 @@ typedef struct {
     double tau;
     int    max_iter;
     double sv_tol;
+    int    wss;        /* 1: the reference's first-order maximal violating pair (code/main3.cpp:107-142).
+                          2: second-order choice of i_low (Fan, Chen, Lin 2005, "working set selection using second order
+                          information", the rule LIBSVM uses); NOT in the reference -- see oracle_smo_train */
 } oracle_params;
 
 /* stop_reason mirrors the reference's loop exits (code/main3.cpp:205,213,246,253,283) */
@@ -81,7 +84,14 @@ int    oracle_calculate_U_V(int s, double a_high, double a_low, double C, double
 /* code/main3.cpp:162-294 (init != 0) and code/mpi_svm_main2.cpp:154-288 (init == 0: alpha is
  * in/out and f is rebuilt from it, :167-183).  trace (optional) receives (i_high, i_low) of every
  * iteration that reached the update, trace_cap pairs at most.  f_out (optional) receives the final
- * error vector.  arith selects ORACLE_ARITH_*.  Returns 0. */
+ * error vector.  arith selects ORACLE_ARITH_*.  Returns 0.
+ *
+ * p->wss == 2 (no counterpart in the reference: PARITY UNPINNED, checked only through the solution it reaches):
+ * i_high, the stop test and every other line stay as above; i_low becomes the row of I_low with f_t > b_high that
+ * maximises (f_t - b_high)^2 / eta_t, eta_t = K11 + K_tt - 2 K(i_high, t) = 2 - 2 K(i_high, t) (the gain of the
+ * two-variable sub-problem, Fan et al. 2005 eq. WSS 2 with a_it = eta_t, b_it = f_t - b_high), lowest index among equal
+ * gains; rows with eta_t <= eps are passed over (the reference's own step would stop on them, :253); if no row qualifies
+ * the first-order i_low stands. */
 int    oracle_smo_train(const double *x, const int *y, size_t n, size_t d,
                         double *alpha, double *b, const oracle_params *p, int init,
                         int arith, oracle_result *res,

@@ -831,7 +831,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     if (!ctx) return SVMB200_EINVAL;
     if (!params || !alpha || !b) FAIL(SVMB200_EINVAL, "params, alpha and b must not be NULL");
     if (!ctx->have_train) FAIL(SVMB200_ESTATE, "svmb200_smo_train called before svmb200_set_train_*");
-    if (params->wss != 1) FAIL(SVMB200_EINVAL, "wss=%d: only the reference's first-order rule (1) exists", params->wss);
+    if (params->wss != 1 && params->wss != 2) FAIL(SVMB200_EINVAL, "wss=%d: 1 (the reference's first-order rule) or 2 (second-order choice of i_low)", params->wss);
     const int CH = resolve_chunk(params->accum_chunk);
     if (CH < 0) FAIL(SVMB200_EINVAL, "accum_chunk must be 0, 1, 2 or 4");
     if (params->max_iter < 1) FAIL(SVMB200_EINVAL, "max_iter must be >= 1");
@@ -847,6 +847,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const int QDEC = q_for_pitch(ctx->dec_pitch4, ctx->dec_f64);      // the decision kernels' row class (warm start)
     // fp32 rows: 8 warps taking rows in groups (SMO_DEFAULT_THREADS); FP64 rows: the same for the longest rows (Q = 13), else 12 warps, a row per step
     int threads = u8 ? SMO_U8_THREADS : ctx->x_f64 ? (Q == 13 ? 256 : 384) : SMO_DEFAULT_THREADS;
+#ifdef SVM_TIMING
+    if (u8 && u8_qt_class(ctx->u8_tw) == 2 && getenv("SVMB200_U8_THREADS")) threads = atoi(getenv("SVMB200_U8_THREADS")) == 384 ? 384 : 256;
+#endif
 #ifdef SVM_TIMING      // measurement knobs exist in the profiling build only (libsvmb200_timing.so): the product reads no environment
     if (ctx->x_f64 && Q == 13 && getenv("SVMB200_F64_ONE_ROW")) threads = 384;
     if (!ctx->x_f64)
@@ -949,6 +952,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     a.abort_word = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * SMO_MAX_RECS * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
     a.n = n; a.pitch4 = ctx->pitch4; a.kslots = kslots; a.cache_cap = cache_cap; a.trace_cap = trace_cap;
     a.max_iter = params->max_iter;
+    a.wss = params->wss;
     a.cache_counter0 = keep ? ctx->cache_counter : 0;
     a.C = params->C; a.gamma = params->gamma; a.eps = params->eps; a.tau = params->tau;
     a.policy_stream = L2_EVICT_FIRST; a.policy_keep = L2_EVICT_LAST; a.keep_per_1024 = 0;
@@ -995,6 +999,10 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     auto launch = [&](int cl) -> cudaError_t {
+#ifdef SVM_TIMING
+        if (u8 && threads == 384)
+            return launch_persistent(smo_persistent_kernel<unsigned char, 8, 2, 384>, a, grid, 384, cl, smem, ctx->stream);
+#endif
         if (u8)
             return dispatch_u8(ctx->u8_tw, [&]<int QM, int QT>() -> cudaError_t {
                 return launch_persistent(smo_persistent_kernel<unsigned char, QM, QT, SMO_U8_THREADS>, a, grid, SMO_U8_THREADS, cl, smem, ctx->stream);

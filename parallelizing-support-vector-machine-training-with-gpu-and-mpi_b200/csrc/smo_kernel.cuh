@@ -64,6 +64,7 @@ struct SmoArgs {
     long long cache_counter0;  // allocation number to start from (> 0 when the cache is kept from an earlier run on the same X)
     int trace_cap;
     int max_iter;
+    int wss;               // 1: first-order pair (the reference); 2: second-order choice of i_low
     double C, gamma, eps, tau;
     unsigned long long policy_stream;  // L2 policy for the streamed part of every CTA's rows
     unsigned long long policy_keep;    // L2 policy for the leading keep_frac of every warp's rows
@@ -193,6 +194,43 @@ __device__ __forceinline__ double u8_kernel_value(const unsigned char *X, int ro
     return svm_exp(-gamma * fma((double)S, wR, tail));
 }
 
+// The lane's partial sums of NR rows of a group against both pivots: word slot by word slot, the rows side by side.
+// SI / P: [pivot * RPS + row].
+template <int QM, int QT, int RPS, int NR>
+__device__ __forceinline__ void u8_group_sums(const unsigned char *lanep, int row_bytes, int tail_off, int qm, int qt, const unsigned (&pm_h)[QM],
+                                              const unsigned (&pm_l)[QM], const double (&pw_h)[QT][4], const double (&pw_l)[QT][4], int (&SI)[2 * RPS],
+                                              double (&P)[2 * RPS])
+{
+#pragma unroll
+    for (int i = 0; i < QM; ++i)
+        if (i < qm) {
+            unsigned w[NR];
+#pragma unroll
+            for (int r = 0; r < NR; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + r * row_bytes + i * 128);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                SI[r] = (int)__dp4a(w[r], pm_h[i], (unsigned)SI[r]);
+                SI[RPS + r] = (int)__dp4a(w[r], pm_l[i], (unsigned)SI[RPS + r]);
+            }
+        }
+#pragma unroll
+    for (int i = 0; i < QT; ++i)
+        if (i < qt) {
+            unsigned w[NR];
+#pragma unroll
+            for (int r = 0; r < NR; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + tail_off + r * row_bytes + i * 128);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+#pragma unroll
+                for (int r = 0; r < NR; ++r) {
+                    const double ud = u8_to_f64(w[r], c);
+                    P[r] = fma(ud, pw_h[i][c], P[r]);
+                    P[RPS + r] = fma(ud, pw_l[i][c], P[RPS + r]);
+                }
+            }
+        }
+}
+
 // membership tests of calc_i_high / calc_i_low (code/main3.cpp:115,134)
 __device__ __forceinline__ bool in_I_high(int y, double a, double C, double eps)
 {
@@ -236,6 +274,55 @@ __device__ __forceinline__ void best_consider(LocalBest &b, long long j, double 
     if (in_I_high(yj, aj, C, eps) && fj < b.lo.f) { b.lo.f = fj; b.lo.idx = (int)j; b.lo.alpha = aj; b.lo.y = yj; b.lo.q = qj; }
     if (in_I_low(yj, aj, C, eps) && fj > b.hi.f) { b.hi.f = fj; b.hi.idx = (int)j; b.hi.alpha = aj; b.hi.y = yj; b.hi.q = qj; }
 }
+// Second-order choice of i_low (svmb200_params.wss = 2; Fan, Chen, Lin 2005 -- not in the reference): among the rows of
+// I_low with f_t > b_high, the one that maximises the gain (f_t - b_high)^2 / eta_t of the two-variable sub-problem,
+// eta_t = 2 - 2 K(i_high, t); rows with eta_t <= eps are passed over; lowest index among equal gains.  Both sides of the
+// candidate elect the same row (min of -gain, max of gain), so that the record also carries f_t (in lo.alpha) next to
+// alpha_t, y_t and the cache number.
+__device__ __forceinline__ void gain_consider(LocalBest &b, long long j, double fj, double aj, int yj, long long qj, double kh, double b_high,
+                                              double C, double eps)
+{
+    if (!in_I_low(yj, aj, C, eps) || !(fj > b_high)) return;
+    const double eta = 1.0 + 1.0 - 2.0 * kh;
+    if (eta <= eps) return;
+    const double diff = fj - b_high;
+    const double gain = diff * diff / eta;
+    if (gain > b.hi.f) {
+        b.hi.f = gain; b.hi.idx = (int)j; b.hi.alpha = aj; b.hi.y = yj; b.hi.q = qj;
+        b.lo.f = -gain; b.lo.idx = (int)j; b.lo.alpha = fj; b.lo.y = yj; b.lo.q = qj;
+    }
+}
+
+// What an iteration's pass does with a row once both kernel values are known.
+struct IterState {
+    double c_h, c_l, na_h, na_l, b_high;
+    long long i_high, i_low, q_h, q_l;
+    int slot_h, slot_l;
+    bool hit_h, hit_l;
+    bool gain;            // the pass only chooses i_low by gain (wss = 2): no f update; kl is a copy of kh
+};
+__device__ __forceinline__ void finish_row(const SmoArgs &a, const IterState &it, long long j, double fj, double aj, int yj, long long qj,
+                                           double kh, double kl, LocalBest &acc)
+{
+    if (it.gain) {
+        if (it.slot_h >= 0 && !it.hit_h) {
+            a.cacheK[(size_t)it.slot_h * a.n + j] = kh;
+            __threadfence();                                     // K12 of the update that follows is read by other CTAs
+            if (j == it.i_high && a.cacheq) { qj = it.q_h; a.cacheq[j] = qj; }
+        }
+        gain_consider(acc, j, fj, aj, yj, qj, kh, it.b_high, a.C, a.eps);
+        return;
+    }
+    fj = fj + (it.c_h * kh + it.c_l * kl);                       // main3.cpp:274
+    a.f[j] = fj;
+    if (it.slot_h >= 0 && !it.hit_h) a.cacheK[(size_t)it.slot_h * a.n + j] = kh;
+    if (it.slot_l >= 0 && !it.hit_l) a.cacheK[(size_t)it.slot_l * a.n + j] = kl;
+    if (it.slot_h >= 0 && !(it.hit_h && it.hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
+    if (j == it.i_high) { aj = it.na_h; a.alpha[j] = aj; if (a.cacheq && !it.hit_h) { qj = it.q_h; a.cacheq[j] = qj; } }
+    if (j == it.i_low) { aj = it.na_l; a.alpha[j] = aj; if (a.cacheq && !it.hit_l) { qj = it.q_l; a.cacheq[j] = qj; } }
+    best_consider(acc, j, fj, aj, yj, qj, a.C, a.eps);
+}
+
 // Warp-wide (value, lowest index) winner with the hardware integer reduction (REDUX): the double is
 // mapped to a 64-bit key whose unsigned order is the double's order, its two halves are reduced one
 // after the other, and the row index breaks ties.  f + 0.0 folds -0.0 into +0.0 so that, as in the
@@ -659,9 +746,12 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     const long long r1 = a.row_begin + (long long)(blockIdx.x + 1) * n_own / G;
     const long long R = r1 - r0;
     // warps take contiguous ranges, cut at multiples of RPS rows from r0 (so only the CTA's last rows form a short group)
-    const long long units = (R + RPS - 1) / RPS;
-    const long long w0 = min(r1, r0 + RPS * ((long long)warp * units / WARPS));
-    const long long w1 = min(r1, r0 + RPS * ((long long)(warp + 1) * units / WARPS));
+    // (uint8 rows: cut at any row -- a warp's last, short group costs half a group when it has up to four rows, so equal row
+    // counts mean equal work)
+    constexpr int CUT = sizeof(XT) == 1 ? 1 : RPS;
+    const long long units = (R + CUT - 1) / CUT;
+    const long long w0 = min(r1, r0 + CUT * ((long long)warp * units / WARPS));
+    const long long w1 = min(r1, r0 + CUT * ((long long)(warp + 1) * units / WARPS));
     const int m = (int)(w1 - w0);
     const int keep_rows = (int)(((long long)m * a.keep_per_1024) >> 10);
 
@@ -713,22 +803,40 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     long long cache_counter = a.cache_counter0;   // replicated: every CTA sees the same hit/miss sequence
     long long x_passes = 0, cache_hits = 0;
 
+    Best lo, hi;                         // the working pair with what the scalar update needs of its rows
+    lo.f = hi.f = lo.alpha = hi.alpha = 0.0; lo.q = hi.q = -1; lo.idx = hi.idx = IDX_NONE; lo.y = hi.y = 0;
+    bool gain = false;                   // wss = 2: the pass at hand only chooses i_low (see gain_consider)
     for (;;) {
         if (!exchange(a, sh, mine, gather_no)) { stop = 5; break; }                 // the one grid-wide synchronisation
-        if (num_iter > a.max_iter) { stop = 4; break; }                             // main3.cpp:283 (b keeps this iteration's b_high/b_low)
-        const Best lo = mine.lo, hi = mine.hi;
-        SVM_STAMP(0);
-        SVM_GSTAMP(0);
-        i_high = lo.idx == IDX_NONE ? a.n : lo.idx;
-        i_low = hi.idx == IDX_NONE ? a.n : hi.idx;
-        if (lo.idx == IDX_NONE || hi.idx == IDX_NONE) { stop = 1; break; }          // main3.cpp:205
-        b_high = lo.f;
-        b_low = hi.f;
-        if (b_low <= b_high + 2.0 * a.tau) { stop = 0; break; }                     // main3.cpp:213
+        if (!gain) {
+            // the exchange that followed an update (or the start): i_high, the first-order i_low, the stop test
+            if (num_iter > a.max_iter) { stop = 4; break; }                         // main3.cpp:283 (b keeps this iteration's b_high/b_low)
+            lo = mine.lo; hi = mine.hi;
+            SVM_STAMP(0);
+            SVM_GSTAMP(0);
+            i_high = lo.idx == IDX_NONE ? a.n : lo.idx;
+            i_low = hi.idx == IDX_NONE ? a.n : hi.idx;
+            if (lo.idx == IDX_NONE || hi.idx == IDX_NONE) { stop = 1; break; }      // main3.cpp:205
+            b_high = lo.f;
+            b_low = hi.f;
+            if (b_low <= b_high + 2.0 * a.tau) { stop = 0; break; }                 // main3.cpp:213
+            gain = a.wss == 2;                                                       // second-order: first a pass that chooses i_low
+        } else {
+            // the exchange that followed a gain pass: the row it elected replaces the first-order i_low (if any row qualified)
+            gain = false;
+            if (mine.hi.idx != IDX_NONE) {
+                hi = mine.hi;
+                hi.f = mine.lo.alpha;                                                // f of that row travelled in the other side
+                i_low = hi.idx;
+                b_low = hi.f;
+            }
+        }
+        // in a gain pass both pivots are row i_high
+        const long long piv_l = gain ? i_high : i_low;
 
         // row-cache lookup (FIFO by allocation number; validity needs no notification)
         bool hit_h = false, hit_l = false;
-        long long q_h = lo.q, q_l = hi.q;
+        long long q_h = lo.q, q_l = gain ? lo.q : hi.q;
         if (a.cache_cap > 0) {
             hit_h = q_h >= 0 && cache_counter - q_h < a.cache_cap;
             hit_l = q_l >= 0 && cache_counter - q_l < a.cache_cap;
@@ -762,7 +870,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         if constexpr (IS_U8) {
           if (!use_cache) {
             const unsigned *xh = reinterpret_cast<const unsigned *>(Xb + (size_t)i_high * row_bytes);
-            const unsigned *xl = reinterpret_cast<const unsigned *>(Xb + (size_t)i_low * row_bytes);
+            const unsigned *xl = reinterpret_cast<const unsigned *>(Xb + (size_t)piv_l * row_bytes);
             unsigned th[QT], tl[QT];
 #pragma unroll
             for (int i = 0; i < QM; ++i) {
@@ -776,8 +884,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 th[i] = w < a.tw ? __ldg(xh + a.mw + w) : 0u;
                 tl[i] = w < a.tw ? __ldg(xl + a.mw + w) : 0u;
             }
-            nm_h = a.nmain[i_high]; nm_l = a.nmain[i_low];
-            n_h = a.ntail[i_high]; n_l = a.ntail[i_low];
+            nm_h = a.nmain[i_high]; nm_l = a.nmain[piv_l];
+            n_h = a.ntail[i_high]; n_l = a.ntail[piv_l];
             SVM_STAMP(15);
             int dot = 0;
 #pragma unroll
@@ -801,6 +909,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             double tail = (n_l + n_h) - 2.0 * acc;
             if (tail < 0.0) tail = 0.0;
             K12 = svm_exp(-a.gamma * fma((double)S, a.wR, tail));
+          } else if (gain) {
+            K12 = 1.0;                                          // not used: a gain pass makes no step
           } else if (i_low >= a.row_begin && i_low < a.row_end) {
             __threadfence();
             K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
@@ -810,14 +920,14 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         } else
         if (!use_cache) {
             const Vec *xh = reinterpret_cast<const Vec *>(a.X) + (size_t)i_high * a.pitch4;
-            const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)i_low * a.pitch4;
+            const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)piv_l * a.pitch4;
 #pragma unroll
             for (int i = 0; i < Q; ++i) {
                 const int q = i * 32 + lane;
                 pv.h[i] = q < a.pitch4 ? __ldg(xh + q) : vec_zero<Vec>();
                 pv.l[i] = q < a.pitch4 ? __ldg(xl + q) : vec_zero<Vec>();
             }
-            if (sizeof(XT) == 4) { n_h = a.sqn[i_high]; n_l = a.sqn[i_low]; }
+            if (sizeof(XT) == 4) { n_h = a.sqn[i_high]; n_l = a.sqn[piv_l]; }
             SVM_STAMP(15);
             double acc = 0.0;
 #pragma unroll
@@ -825,6 +935,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 if (i * 32 + lane < a.pitch4) accum_pair<CH>(pv.l[i], pv.h[i], acc);
             acc = warp_sum_butterfly(acc);
             K12 = svm_exp(-a.gamma * dist2<XT>(n_h, n_l, acc));
+        } else if (gain) {
+            K12 = 1.0;                                              // not used: a gain pass makes no step
         } else if (i_low >= a.row_begin && i_low < a.row_end) {
             // the one read of a value another CTA wrote: column i_low of the cached row was stored by the CTA that
             // owns row i_low, at least one exchange ago (its __threadfence below, this thread's fence here after the
@@ -835,7 +947,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             // row sharding: column i_low of the cached rows lives on the GPU that owns row i_low; X is
             // replicated, so form K12 here the way that GPU formed it (same code, same bits)
             const Vec *xh = reinterpret_cast<const Vec *>(a.X) + (size_t)i_high * a.pitch4;
-            const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)i_low * a.pitch4;
+            const Vec *xl = reinterpret_cast<const Vec *>(a.X) + (size_t)piv_l * a.pitch4;
             double acc = 0.0;
 #pragma unroll
             for (int i = 0; i < Q; ++i) {
@@ -847,11 +959,16 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         }
 
         // scalar update, main3.cpp:235-270, operation for operation
-        const PairStep ps = pair_update(lo.y, hi.y, lo.alpha, hi.alpha, b_high, b_low, K12, a.C, a.eps);
-        if (ps.stop) { stop = ps.stop; break; }                 // main3.cpp:246 / :253
-        const double na_h = ps.na_h, na_l = ps.na_l, c_h = ps.c_h, c_l = ps.c_l;
+        IterState it;
+        it.gain = gain; it.b_high = b_high; it.i_high = i_high; it.i_low = i_low;
+        it.c_h = it.c_l = 0.0; it.na_h = lo.alpha; it.na_l = hi.alpha;
+        if (!gain) {
+            const PairStep ps = pair_update(lo.y, hi.y, lo.alpha, hi.alpha, b_high, b_low, K12, a.C, a.eps);
+            if (ps.stop) { stop = ps.stop; break; }             // main3.cpp:246 / :253
+            it.na_h = ps.na_h; it.na_l = ps.na_l; it.c_h = ps.c_h; it.c_l = ps.c_l;
+        }
 
-        if (blockIdx.x == 0 && threadIdx.x == 0 && a.rank == 0 && num_iter - 1 < a.trace_cap) {
+        if (!gain && blockIdx.x == 0 && threadIdx.x == 0 && a.rank == 0 && num_iter - 1 < a.trace_cap) {
             a.trace[2 * (num_iter - 1)] = (int)i_high;
             a.trace[2 * (num_iter - 1) + 1] = (int)i_low;
         }
@@ -861,11 +978,14 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         if (a.cache_cap > 0) {
             if (!use_cache) {
                 if (!hit_h) q_h = cache_counter++;
-                if (!hit_l) q_l = cache_counter++;
+                if (gain) q_l = q_h;                          // one row, computed twice over
+                else if (!hit_l) q_l = cache_counter++;
             }
             slot_h = (int)(q_h % a.cache_cap);
             slot_l = (int)(q_l % a.cache_cap);
+            if (gain) { hit_l = true; lo.q = q_h; }           // nothing is stored for the copy; the update that follows finds row i_high cached
         }
+        it.q_h = q_h; it.q_l = q_l; it.slot_h = slot_h; it.slot_l = slot_l; it.hit_h = hit_h; it.hit_l = hit_l;
 
         LocalBest acc_best;
         best_init(acc_best);
@@ -896,67 +1016,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     double P[2 * RPS];                     // the same for the weighted tail
 #pragma unroll
                     for (int k = 0; k < 2 * RPS; ++k) { SI[k] = 0; P[k] = 0.0; }
+                    // eight rows side by side (sixteen independent sums), or four when the group is the short one that ends the
+                    // warp's range: rows beyond the group's last hold bytes of an earlier group, their sums are never read
                     const unsigned char *lanep = grp + lane * 4;
-                    if (rows_here == RPS) {
-                        // a full group: word slot by word slot, the eight rows side by side (sixteen independent sums)
-#pragma unroll
-                        for (int i = 0; i < QM; ++i)
-                            if (i < qm) {
-                                unsigned w[RPS];
-#pragma unroll
-                                for (int r = 0; r < RPS; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + r * row_bytes + i * 128);
-#pragma unroll
-                                for (int r = 0; r < RPS; ++r) {
-                                    SI[r] = (int)__dp4a(w[r], pm_h[i], (unsigned)SI[r]);
-                                    SI[RPS + r] = (int)__dp4a(w[r], pm_l[i], (unsigned)SI[RPS + r]);
-                                }
-                            }
-#pragma unroll
-                        for (int i = 0; i < QT; ++i)
-                            if (i < qt) {
-                                unsigned w[RPS];
-#pragma unroll
-                                for (int r = 0; r < RPS; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + tail_off + r * row_bytes + i * 128);
-#pragma unroll
-                                for (int c = 0; c < 4; ++c) {
-#pragma unroll
-                                    for (int r = 0; r < RPS; ++r) {
-                                        const double ud = u8_to_f64(w[r], c);
-                                        P[r] = fma(ud, pw_h[i][c], P[r]);
-                                        P[RPS + r] = fma(ud, pw_l[i][c], P[RPS + r]);
-                                    }
-                                }
-                            }
-                    } else {
-                        // the short group at the end of a CTA's rows
-                        for (int r = 0; r < rows_here; ++r) {
-                            const unsigned char *rowp = lanep + (size_t)r * row_bytes;
-                            int sh_ = 0, sl_ = 0;
-                            double th_ = 0.0, tl_ = 0.0;
-#pragma unroll
-                            for (int i = 0; i < QM; ++i)
-                                if (i < qm) {
-                                    const unsigned w = *reinterpret_cast<const unsigned *>(rowp + i * 128);
-                                    sh_ = (int)__dp4a(w, pm_h[i], (unsigned)sh_);
-                                    sl_ = (int)__dp4a(w, pm_l[i], (unsigned)sl_);
-                                }
-#pragma unroll
-                            for (int i = 0; i < QT; ++i)
-                                if (i < qt) {
-                                    const unsigned w = *reinterpret_cast<const unsigned *>(rowp + tail_off + i * 128);
-#pragma unroll
-                                    for (int c = 0; c < 4; ++c) {
-                                        const double ud = u8_to_f64(w, c);
-                                        th_ = fma(ud, pw_h[i][c], th_);
-                                        tl_ = fma(ud, pw_l[i][c], tl_);
-                                    }
-                                }
-                            // P[] / SI[] are indexed with constants only (they live in registers)
-#pragma unroll
-                            for (int k = 0; k < RPS; ++k)
-                                if (k == r) { SI[k] = sh_; SI[RPS + k] = sl_; P[k] = th_; P[RPS + k] = tl_; }
-                        }
-                    }
+                    if (rows_here > 4) u8_group_sums<QM, QT, RPS, 8>(lanep, row_bytes, tail_off, qm, qt, pm_h, pm_l, pw_h, pw_l, SI, P);
+                    else u8_group_sums<QM, QT, RPS, 4>(lanep, row_bytes, tail_off, qm, qt, pm_h, pm_l, pw_h, pw_l, SI, P);
                     __syncwarp();
                     fence_proxy_async();
                     issue_into(cslot);
@@ -1008,14 +1072,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     if (t_l < 0.0) t_l = 0.0;
                     const double kh = svm_exp(-a.gamma * fma((double)(nmj + nm_h - 2 * ii.x), a.wR, t_h));
                     const double kl = svm_exp(-a.gamma * fma((double)(nmj + nm_l - 2 * ii.y), a.wR, t_l));
-                    fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
-                    a.f[j] = fj;
-                    if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
-                    if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
-                    if (slot_h >= 0 && !(hit_h && hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
-                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
-                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
-                    best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                    finish_row(a, it, j, fj, aj, yj, qj, kh, kl, acc_best);
                 }
                 __syncwarp();                                  // the parked sums have been read: the next block may overwrite them
               }
@@ -1129,14 +1186,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     const double2 dd = stage[lane];
                     const double kh = svm_exp(-a.gamma * dist2<XT>(n_h, nj, dd.x));
                     const double kl = svm_exp(-a.gamma * dist2<XT>(n_l, nj, dd.y));
-                    fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
-                    a.f[j] = fj;
-                    if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
-                    if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
-                    if (slot_h >= 0 && !(hit_h && hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
-                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
-                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
-                    best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                    finish_row(a, it, j, fj, aj, yj, qj, kh, kl, acc_best);
                 }
                 __syncwarp();                                  // the parked sums have been read: the next block may overwrite them
               }
@@ -1165,19 +1215,12 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 if (lane < cnt) {
                     const double kh = svm_exp(-a.gamma * dist2<XT>(n_h, nj, my_dh));
                     const double kl = svm_exp(-a.gamma * dist2<XT>(n_l, nj, my_dl));
-                    fj = fj + (c_h * kh + c_l * kl);            // main3.cpp:274
-                    a.f[j] = fj;
-                    if (slot_h >= 0 && !hit_h) a.cacheK[(size_t)slot_h * a.n + j] = kh;
-                    if (slot_l >= 0 && !hit_l) a.cacheK[(size_t)slot_l * a.n + j] = kl;
-                    if (slot_h >= 0 && !(hit_h && hit_l)) __threadfence();   // K12 of a later cached iteration is read by other CTAs
-                    if (j == i_high) { aj = na_h; a.alpha[j] = aj; if (a.cacheq && !hit_h) { qj = q_h; a.cacheq[j] = qj; } }
-                    if (j == i_low) { aj = na_l; a.alpha[j] = aj; if (a.cacheq && !hit_l) { qj = q_l; a.cacheq[j] = qj; } }
-                    best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                    finish_row(a, it, j, fj, aj, yj, qj, kh, kl, acc_best);
                 }
             }
         } else {
             // ---------------- cached pass: a thread per row over two cached kernel rows ----------------
-            ++cache_hits;
+            if (!gain) ++cache_hits;
             const double *kh_row = a.cacheK + (size_t)slot_h * a.n;
             const double *kl_row = a.cacheK + (size_t)slot_l * a.n;
             for (long long j = pj; j < r1; j += THREADS) {
@@ -1186,11 +1229,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 const int yj = first ? p_y : second ? p2_y : a.y[j];
                 const long long qj = first ? p_q : second ? p2_q : a.cacheq[j];
                 const double khj = first ? p_kh : second ? p2_kh : kh_row[j], klj = first ? p_kl : second ? p2_kl : kl_row[j];
-                fj = fj + (c_h * khj + c_l * klj);
-                a.f[j] = fj;
-                if (j == i_high) { aj = na_h; a.alpha[j] = aj; }
-                if (j == i_low) { aj = na_l; a.alpha[j] = aj; }
-                best_consider(acc_best, j, fj, aj, yj, qj, a.C, a.eps);
+                finish_row(a, it, j, fj, aj, yj, qj, khj, klj, acc_best);
             }
         }
 
@@ -1198,7 +1237,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         SVM_GSTAMP(2);
         ++gather_no;
         mine = acc_best;
-        ++num_iter;                                              // main3.cpp:281
+        if (!gain) ++num_iter;                                   // main3.cpp:281
     }
 
     // drain the ring: every requested copy must land before the CTA may exit

@@ -307,7 +307,7 @@ def test_errors_are_reported(pkg):
     s.set_train_f64(X, y)
     s.n = 8
     with pytest.raises(pkg.SvmB200Error, match="wss"):
-        s.smo_train(wss=2)
+        s.smo_train(wss=3)
     s.close()
 
 

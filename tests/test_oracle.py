@@ -163,3 +163,41 @@ def test_dataset_prefix_property(pkg):
     assert np.array_equal(a[:300], b) and np.array_equal(da[:300], db)
     nz = (a > 0).mean()
     assert 0.1 < nz < 0.35
+
+
+@pytest.mark.parametrize("n", [256, 2000])
+def test_u8_arithmetic_walks_the_reference_pair_sequence(O, dataset, n):
+    """ORACLE_ARITH_DEVICE_U8 (exact integer sums over the features of the most frequent range, weighted FP64 sums over
+    the rest) against the fixture of the unmodified reference: the kernel values agree to ~1e-16 and the solver selects the
+    same pairs, iteration for iteration."""
+    g = golden(n)
+    X, _, y = dataset(n)
+    R, M, T = O.u8_bind(X)
+    assert R == 255 and M >= 32 and M + T <= 784
+    xs, _, _ = O.scale(X)
+    rng = np.random.default_rng(n)
+    for _ in range(300):
+        i, j = (int(v) for v in rng.integers(0, n, 2))
+        ref = O.lib().oracle_kernel(xs[i], xs[j], 784, 0.00125)
+        assert abs(O.u8_kernel(j, i) - ref) <= 4e-16 * ref
+    assert O.u8_kernel(7, 7) == 1.0
+    out = O.smo_train(xs, y, arith=O.ARITH_DEVICE_U8, trace_cap=4096)
+    assert out["num_iter"] == int(g["num_iter"])
+    assert np.array_equal(out["trace"], g["trace"][:len(out["trace"])])
+    assert np.array_equal(O.sv_indices(out["alpha"]), g["sv_ids"])
+    assert abs(out["b"] - float(g["b"])) <= 1e-12 * max(1.0, abs(float(g["b"])))
+
+
+def test_second_order_selection_restatement(O, dataset):
+    """wss = 2 has no counterpart in the reference (parity unpinned): it must reach the first-order rule's support-vector
+    set and bias (to the stop tolerance) in fewer iterations, and never pick a pair the update would stop on."""
+    X, _, y = dataset(1200)
+    xs, _, _ = O.scale(X)
+    one = O.smo_train(xs, y)
+    two = O.smo_train(xs, y, params=O.default_params(wss=2), trace_cap=100000)
+    assert two["stop_reason"] == 0 and two["num_iter"] < one["num_iter"]
+    assert np.array_equal(O.sv_indices(two["alpha"]), O.sv_indices(one["alpha"]))
+    assert abs(two["b"] - one["b"]) <= 1e-4 * max(1.0, abs(one["b"]))
+    assert np.max(np.abs(two["alpha"] - one["alpha"])) <= 1e-3 * 10.0
+    # the first pair: i_high as in the first-order rule, i_low by gain
+    assert two["trace"][0][0] == one["i_high"] or two["trace"][0][0] == O.smo_train(xs, y, params=O.default_params(max_iter=1))["i_high"]
