@@ -240,10 +240,10 @@ double oracle_device_kernel_f64(const double *a, const double *b, size_t d, doub
  *     d2 = S_main * w_R + tail
  *   S_main = sum over the features whose range is the most frequent one, R, of (u_k - p_k)^2 : exact integer
  *   tail   = (N(u) + N(p)) - 2 D(u, p) over the other non-constant features, clamped at 0, with
- *            D(u, p) = sum_k u_k * (w_k p_k), N(u) = D(u, u), w_k = (1/range_k)^2, in FP64: lane l = g mod 32 owns
- *            the 4-byte words g of the tail, adds its elements in order with fma, and the 32 lane sums are
- *            combined by the xor-butterfly 16,8,4,2,1.  D's first argument is the streamed row, the second
- *            the pivot row.
+ *            D(u, p) = sum_k u_k * (w_k p_k), N(u) = D(u, u), w_k = (1/range_k)^2, in FP64 as (D_0 + D_1) + (D_2 + D_3)
+ *            where D_c adds the features of the 4-byte words w = c (mod 4) of the tail in ascending order with fma (the device walks only the
+ *            positions where a pivot byte is non-zero: a zero byte adds +0).  D's first argument is the streamed row,
+ *            the second the pivot row.
  * Constant features (range 0) contribute (u_k - p_k) = 0 and are left out.  K = exp(-gamma d2) (oracle_device_exp).
  * ------------------------------------------------------------------------------------------ */
 static struct {
@@ -259,19 +259,12 @@ static struct {
 
 static double u8_tail_dot(const uint8_t *row, const uint8_t *piv)
 {
-    double lane[32];
-    for (int l = 0; l < 32; ++l) lane[l] = 0.0;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
     for (size_t k = 0; k < g_u8.T; ++k) {
-        size_t g = k / 4;            /* 4-byte word of the tail */
         double pw = g_u8.wt[k] * (double)piv[k];
-        lane[g & 31] = fma((double)row[k], pw, lane[g & 31]);
+        acc[(k >> 2) & 3] = fma((double)row[k], pw, acc[(k >> 2) & 3]);
     }
-    for (int off = 16; off >= 1; off >>= 1) {
-        double t[32];
-        for (int l = 0; l < 32; ++l) t[l] = lane[l] + lane[l ^ off];
-        for (int l = 0; l < 32; ++l) lane[l] = t[l];
-    }
-    return lane[0];
+    return (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 
 void oracle_u8_unbind(void)

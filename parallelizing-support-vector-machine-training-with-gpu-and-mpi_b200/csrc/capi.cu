@@ -27,6 +27,12 @@ extern "C" int svmb200_debug_timing(long long *out, int rows)
     if (!g_timing_dev) return -1;
     return cudaMemcpy(out, g_timing_dev, (size_t)rows * 16 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
 }
+// per-iteration cycle sums of warp 0's pass phases (uint8 rows): wait for data, main sums, tail, refill, integer reduce, finish
+extern "C" int svmb200_debug_timing_pass(long long *out, int rows)
+{
+    if (!g_timing_dev) return -1;
+    return cudaMemcpy(out, g_timing_dev + 4096 * 16 + 8 * 160 * 4, (size_t)rows * 8 * sizeof(long long), cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -2;
+}
 extern "C" int svmb200_debug_timing_grid(long long *out)
 {
     if (!g_timing_dev) return -1;
@@ -350,19 +356,6 @@ static int ingest(svmb200_ctx *ctx, const T *X_host, long long rows, bool comput
     return 0;
 }
 
-// uint8 storage: how many words per lane the tail takes (a template parameter of the kernels: 2, 4 or 8)
-static int u8_qt_class(int tw) { return tw <= 64 ? 2 : tw <= 128 ? 4 : 8; }
-
-template <typename F>
-static cudaError_t dispatch_u8(int tw, F &&fn)
-{
-    switch (u8_qt_class(tw)) {
-    case 2: return fn.template operator()<8, 2>();
-    case 4: return fn.template operator()<8, 4>();
-    default: return fn.template operator()<8, 8>();
-    }
-}
-
 // uint8 storage: the statistics are on the device (ctx->minv / maxv) and the raw rows in scratch at `raw`.  Lays the row
 // out as [main class | tail] (smo_kernel.cuh "uint8 rows"), packs every row that way and forms the per-row norms.
 static int pack_u8_rows(svmb200_ctx *ctx, const unsigned char *raw, long long n)
@@ -413,11 +406,9 @@ static int pack_u8_rows(svmb200_ctx *ctx, const unsigned char *raw, long long n)
     u8_pack_kernel<<<(int)std::min<long long>((words + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
         raw, n, d, row_bytes, ctx->u8_src, static_cast<unsigned char *>(ctx->X));
     CK(cudaGetLastError());
-    CK(dispatch_u8(tw, [&]<int QM, int QT>() -> cudaError_t {
-        u8_norms_kernel<QM, QT><<<(unsigned)((n * 32 + 255) / 256), 256, 0, ctx->stream>>>(
-            static_cast<const unsigned char *>(ctx->X), n, row_bytes, mw, tw, ctx->u8_wt, ctx->u8_nmain, ctx->u8_ntail);
-        return cudaGetLastError();
-    }));
+    u8_norms_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(static_cast<const unsigned char *>(ctx->X), n, row_bytes, mw, tw, ctx->u8_wt,
+                                                                             ctx->u8_nmain, ctx->u8_ntail);
+    CK(cudaGetLastError());
     ctx->launches += 2;
     CK(cudaStreamSynchronize(ctx->stream));      // src / pos / wt are host temporaries
     return 0;
@@ -848,7 +839,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     // fp32 rows: 8 warps taking rows in groups (SMO_DEFAULT_THREADS); FP64 rows: the same for the longest rows (Q = 13), else 12 warps, a row per step
     int threads = u8 ? SMO_U8_THREADS : ctx->x_f64 ? (Q == 13 ? 256 : 384) : SMO_DEFAULT_THREADS;
 #ifdef SVM_TIMING
-    if (u8 && u8_qt_class(ctx->u8_tw) == 2 && getenv("SVMB200_U8_THREADS")) threads = atoi(getenv("SVMB200_U8_THREADS")) == 384 ? 384 : 256;
+    if (u8 && getenv("SVMB200_U8_THREADS")) { const int t = atoi(getenv("SVMB200_U8_THREADS")); threads = (t == 384 || t == 512) ? t : 256; }
 #endif
 #ifdef SVM_TIMING      // measurement knobs exist in the profiling build only (libsvmb200_timing.so): the product reads no environment
     if (ctx->x_f64 && Q == 13 && getenv("SVMB200_F64_ONE_ROW")) threads = 384;
@@ -981,8 +972,8 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 #ifdef SVM_TIMING
     {
         static long long *tbuf = nullptr;
-        if (!tbuf) CK(cudaMalloc(&tbuf, (4096 * 16 + 8 * 160 * 4) * sizeof(long long)));
-        CK(cudaMemsetAsync(tbuf, 0, (4096 * 16 + 8 * 160 * 4) * sizeof(long long), ctx->stream));
+        if (!tbuf) CK(cudaMalloc(&tbuf, (4096 * 16 + 8 * 160 * 4 + 4096 * 8) * sizeof(long long)));
+        CK(cudaMemsetAsync(tbuf, 0, (4096 * 16 + 8 * 160 * 4 + 4096 * 8) * sizeof(long long), ctx->stream));
         a.timing = tbuf; a.timing_cap = 4096;
         g_timing_dev = tbuf;
     }
@@ -1001,12 +992,11 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     auto launch = [&](int cl) -> cudaError_t {
 #ifdef SVM_TIMING
         if (u8 && threads == 384)
-            return launch_persistent(smo_persistent_kernel<unsigned char, 8, 2, 384>, a, grid, 384, cl, smem, ctx->stream);
+            return launch_persistent(smo_persistent_kernel<unsigned char, 8, 1, 384>, a, grid, 384, cl, smem, ctx->stream);
+        if (u8 && threads == 512)
+            return launch_persistent(smo_persistent_kernel<unsigned char, 8, 1, 512>, a, grid, 512, cl, smem, ctx->stream);
 #endif
-        if (u8)
-            return dispatch_u8(ctx->u8_tw, [&]<int QM, int QT>() -> cudaError_t {
-                return launch_persistent(smo_persistent_kernel<unsigned char, QM, QT, SMO_U8_THREADS>, a, grid, SMO_U8_THREADS, cl, smem, ctx->stream);
-            });
+        if (u8) return launch_persistent(smo_persistent_kernel<unsigned char, 8, 1, SMO_U8_THREADS>, a, grid, SMO_U8_THREADS, cl, smem, ctx->stream);
         return launch_smo_any(KernelKey{ctx->x_f64, Q, CH, threads}, a, grid, cl, smem, ctx->stream);
     };
     cudaError_t le = launch(cluster);
@@ -1479,14 +1469,12 @@ int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_
     if (int rc = ensure_scratch(ctx, (size_t)ctx->n * sizeof(double))) return rc;
     double *out = static_cast<double *>(ctx->scratch);
     cudaError_t e;
-    if (ctx->x_u8)
-        e = dispatch_u8(ctx->u8_tw, [&]<int QM, int QT>() -> cudaError_t {
-            u8_kernel_row_kernel<QM, QT><<<(unsigned)((ctx->n * 32 + 255) / 256), 256, 0, ctx->stream>>>(
-                static_cast<const unsigned char *>(ctx->X), ctx->n, ctx->pitch4 * 16, ctx->u8_mw, ctx->u8_tw, ctx->u8_wt, ctx->u8_wR, ctx->u8_nmain,
-                ctx->u8_ntail, i, gamma, out);
-            return cudaGetLastError();
-        });
-    else
+    if (ctx->x_u8) {
+        u8_kernel_row_kernel<<<(unsigned)((ctx->n + 127) / 128), 128, 0, ctx->stream>>>(
+            static_cast<const unsigned char *>(ctx->X), ctx->n, ctx->pitch4 * 16, ctx->u8_mw, ctx->u8_tw, ctx->u8_wt, ctx->u8_wR, ctx->u8_nmain,
+            ctx->u8_ntail, i, gamma, out);
+        e = cudaGetLastError();
+    } else
         e = launch_krow_any(KernelKey{ctx->x_f64, q_for_pitch(ctx->pitch4, ctx->x_f64), CH, 0}, ctx->X, ctx->x_f64 ? nullptr : ctx->sqn,
                             ctx->n, ctx->pitch4, i, gamma, out, ctx->stream);
     ctx->launches += 1;

@@ -154,52 +154,82 @@ __device__ __forceinline__ void group_dot2(const unsigned char *grp, int row_byt
 //     d2 = S_main * w_R + tail
 //   S_main = sum over the features whose range is the most frequent one (R) of (u_k - p_k)^2, an exact integer formed as
 //            |u|^2 + |p|^2 - 2 u.p with four products per IDP4A;
-//   tail   = (N(u) + N(p)) - 2 D(u, p) over the other non-constant features, D(u, p) = sum_k u_k * (w_k p_k) in FP64:
-//            lane l owns the words l, l + 32, ... of the tail, adds its bytes in order with fma, and the lane sums are
-//            combined in xor-butterfly order; N(u) = D(u, u), so duplicates are at distance exactly 0.
-// A byte becomes a double by placing it in the mantissa of 2^52 and subtracting 2^52 (exact, no conversion unit).
-__device__ __forceinline__ double u8_to_f64(unsigned w, int c)
+//   tail   = (N(u) + N(p)) - 2 D(u, p) over the other non-constant features, D(u, p) = sum_k u_k * (w_k p_k) in FP64,
+//            as (D_0 + D_1) + (D_2 + D_3) where D_c adds, in ascending order with fma, the features of the 4-byte words
+//            w = c (mod 4) of the tail;
+//            N(u) = D(u, u), so duplicates are at distance exactly 0.
+// A zero byte of the pivot adds u_k * 0 = +0 to its partial sum, i.e. nothing: the pass therefore walks only the tail
+// positions where one of the two pivots is non-zero (MNIST's border pixels: a handful out of 233), from four sub-lists
+// (one per c) that every warp builds at the top of the iteration.
+struct U8Lists {
+    double2 *pp;            // [4][tw] weighted pivot bytes {w_k p_high_k, w_k p_low_k}
+    unsigned short *kk;     // [4][tw] tail position k
+    unsigned char *xlt;     // [4 * tw] tail bytes of the low pivot (the "row" of K12)
+    int tw;
+};
+// Every warp calls this with the same arguments and writes the same values (no CTA barrier needed: a warp reads what it
+// wrote itself).  Sub-list c holds the positions of the words w = c (mod 4), i.e. of the lanes l = c (mod 4), in ascending
+// order; returns the length of the sub-list of this lane's class, lane & 3 (the sub-list the lane walks later).
+__device__ __forceinline__ int u8_build_lists(const unsigned *__restrict__ xh_tail, const unsigned *__restrict__ xl_tail, const double *sh_wt,
+                                              const U8Lists &L, int lane)
 {
-    return __hiloint2double(0x43300000, (int)__byte_perm(w, 0u, 0x4440u + (unsigned)c)) - 4503599627370496.0;
-}
-// K(row, piv) straight from global memory by one warp (same sums in the same order as the pass)
-template <int QM, int QT>
-__device__ __forceinline__ double u8_kernel_value(const unsigned char *X, int row_bytes, int mw, int tw, const double *__restrict__ wt, double wR,
-                                                  const int *__restrict__ nmain, const double *__restrict__ ntail, long long row, long long piv,
-                                                  double gamma, int lane)
-{
-    const unsigned *xr = reinterpret_cast<const unsigned *>(X + (size_t)row * row_bytes);
-    const unsigned *xp = reinterpret_cast<const unsigned *>(X + (size_t)piv * row_bytes);
-    int dot = 0;
+    const int c = lane & 3;
+    const unsigned before = (0x11111111u << c) & ((1u << lane) - 1u);      // lower lanes of this lane's class
+    const unsigned cls = 0x11111111u << c;
+    int base = 0;                                                          // entries of this class so far
+    for (int w0 = 0; w0 < L.tw; w0 += 32) {
+        const int w = w0 + lane;                                           // tw is a multiple of 32
+        const unsigned th = __ldg(xh_tail + w), tl = __ldg(xl_tail + w);
+        reinterpret_cast<unsigned *>(L.xlt)[w] = tl;
+        int e = c * L.tw + base, total = 0;
+        bool nz[4];
+        unsigned ballot[4];
 #pragma unroll
-    for (int i = 0; i < QM; ++i) {
-        const int w = i * 32 + lane;
-        if (w < mw) dot = __dp4a(__ldg(xr + w), __ldg(xp + w), (unsigned)dot);
-    }
-    dot = __reduce_add_sync(FULL, dot);
-    double acc = 0.0;
-#pragma unroll
-    for (int i = 0; i < QT; ++i) {
-        const int w = i * 32 + lane;
-        if (w < tw) {
-            const unsigned ur = __ldg(xr + mw + w), up = __ldg(xp + mw + w);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) acc = fma(u8_to_f64(ur, c), wt[4 * w + c] * u8_to_f64(up, c), acc);
+        for (int b = 0; b < 4; ++b) {
+            nz[b] = (((th | tl) >> (8 * b)) & 255u) != 0u;
+            ballot[b] = __ballot_sync(FULL, nz[b]);
+            e += __popc(ballot[b] & before);                               // all bytes of the lower lanes come first
+            total += __popc(ballot[b] & cls);
         }
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+            if (nz[b]) {
+                const double wk = sh_wt[4 * w + b];
+                L.kk[e] = (unsigned short)(4 * w + b);
+                L.pp[e] = make_double2(wk * (double)((th >> (8 * b)) & 255u), wk * (double)((tl >> (8 * b)) & 255u));
+                ++e;
+            }
+        base += total;
     }
-    acc = warp_sum_butterfly(acc);
-    const int S = nmain[row] + nmain[piv] - 2 * dot;
-    double tail = (ntail[row] + ntail[piv]) - 2.0 * acc;
-    if (tail < 0.0) tail = 0.0;
-    return svm_exp(-gamma * fma((double)S, wR, tail));
+    __syncwarp();
+    return base;
 }
-
-// The lane's partial sums of NR rows of a group against both pivots: word slot by word slot, the rows side by side.
-// SI / P: [pivot * RPS + row].
-template <int QM, int QT, int RPS, int NR>
-__device__ __forceinline__ void u8_group_sums(const unsigned char *lanep, int row_bytes, int tail_off, int qm, int qt, const unsigned (&pm_h)[QM],
-                                              const unsigned (&pm_l)[QM], const double (&pw_h)[QT][4], const double (&pw_l)[QT][4], int (&SI)[2 * RPS],
-                                              double (&P)[2 * RPS])
+// D(row, pivots) for the row whose tail bytes start at `rowtail` (shared memory): the lane walks sub-list c = lane & 3
+// (`n` entries), the four lanes of a row then form (D_0 + D_1) + (D_2 + D_3).  Whole warp; n = 0 for a lane whose row does
+// not exist.
+__device__ __forceinline__ void u8_tail_dots(const unsigned char *rowtail, int n, const U8Lists &L, int lane, double &dh, double &dl)
+{
+    const int c = lane & 3;
+    const double2 *pp = L.pp + c * L.tw;
+    const unsigned short *kk = L.kk + c * L.tw;
+    double ah = 0.0, al = 0.0;
+    for (int e = 0; e < n; ++e) {
+        const double ud = (double)rowtail[kk[e]];
+        const double2 p = pp[e];
+        ah = fma(ud, p.x, ah);
+        al = fma(ud, p.y, al);
+    }
+    __syncwarp();
+    ah = ah + __shfl_xor_sync(FULL, ah, 1);
+    al = al + __shfl_xor_sync(FULL, al, 1);
+    dh = ah + __shfl_xor_sync(FULL, ah, 2);
+    dl = al + __shfl_xor_sync(FULL, al, 2);
+}
+// The lane's partial integer dot products of NR rows of a group against both pivots over the main class: word slot by
+// word slot, the rows side by side.  SI: [pivot * RPS + row].
+template <int QM, int RPS, int NR>
+__device__ __forceinline__ void u8_main_sums(const unsigned char *lanep, int row_bytes, int qm, const unsigned (&pm_h)[QM], const unsigned (&pm_l)[QM],
+                                             int (&SI)[2 * RPS])
 {
 #pragma unroll
     for (int i = 0; i < QM; ++i)
@@ -211,22 +241,6 @@ __device__ __forceinline__ void u8_group_sums(const unsigned char *lanep, int ro
             for (int r = 0; r < NR; ++r) {
                 SI[r] = (int)__dp4a(w[r], pm_h[i], (unsigned)SI[r]);
                 SI[RPS + r] = (int)__dp4a(w[r], pm_l[i], (unsigned)SI[RPS + r]);
-            }
-        }
-#pragma unroll
-    for (int i = 0; i < QT; ++i)
-        if (i < qt) {
-            unsigned w[NR];
-#pragma unroll
-            for (int r = 0; r < NR; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + tail_off + r * row_bytes + i * 128);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-#pragma unroll
-                for (int r = 0; r < NR; ++r) {
-                    const double ud = u8_to_f64(w[r], c);
-                    P[r] = fma(ud, pw_h[i][c], P[r]);
-                    P[RPS + r] = fma(ud, pw_l[i][c], P[RPS + r]);
-                }
             }
         }
 }
@@ -537,7 +551,14 @@ struct __align__(16) Shared {
 #define SVM_STAMP(k) SVM_STAMP_T(k, 0)
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define SVM_GSTAMP(k) do { if (a.timing && threadIdx.x == 0 && gather_no >= 100 && gather_no < 108) a.timing[(size_t)a.timing_cap * 16 + ((size_t)(gather_no - 100) * gridDim.x + blockIdx.x) * 4 + (k)] = (long long)gtimer(); } while (0)
+// cycle sums of the pass phases of CTA 0's warp 0 (profiles/timeline_pass.py)
+#define SVM_PH_DECL long long ph_t = clock64(), ph_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define SVM_PH(k) do { const long long now_ = clock64(); ph_acc[k] += now_ - ph_t; ph_t = now_; } while (0)
+#define SVM_PH_FLUSH do { if (a.timing && blockIdx.x == 0 && threadIdx.x == 0 && gather_no < a.timing_cap) for (int k_ = 0; k_ < 8; ++k_) a.timing[(size_t)a.timing_cap * 16 + 8 * 160 * 4 + (size_t)gather_no * 8 + k_] = ph_acc[k_]; } while (0)
 #else
+#define SVM_PH_DECL do { } while (0)
+#define SVM_PH(k) do { } while (0)
+#define SVM_PH_FLUSH do { } while (0)
 #define SVM_STAMP_T(k, tid) do { } while (0)
 #define SVM_STAMP(k) do { } while (0)
 #define SVM_GSTAMP(k) do { } while (0)
@@ -735,8 +756,13 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     double2 *stage = stage_all + warp * 32;
     // (uint8 rows) per warp: the two integer sums of each of the 32 rows of a block; then the tail weights, shared by the CTA
     constexpr bool IS_U8 = sizeof(XT) == 1;
-    constexpr int QM = IS_U8 ? Q : 1, QT = IS_U8 ? CH : 1;       // words per lane of the main class / of the tail
+    constexpr int QM = IS_U8 ? Q : 1;                             // words per lane of the main class
     double *sh_wt = reinterpret_cast<double *>(reinterpret_cast<int2 *>(stage_all + WARPS * 32) + WARPS * 32);
+    U8Lists lists;
+    lists.tw = a.tw;
+    lists.pp = reinterpret_cast<double2 *>(sh_wt + a.tw * 4);
+    lists.kk = reinterpret_cast<unsigned short *>(lists.pp + a.tw * 4);
+    lists.xlt = reinterpret_cast<unsigned char *>(lists.kk + a.tw * 4);
     if constexpr (IS_U8)
         for (int k = threadIdx.x; k < a.tw * 4; k += THREADS) sh_wt[k] = a.wt[k];
 
@@ -863,59 +889,42 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         // K12 = K(i_high, i_low)  (main3.cpp:241)
         Pivots<Vec, Q> pv;
         double K12, n_h = 0.0, n_l = 0.0;
-        // uint8 rows: the pivots' main-class words as they are, their tail bytes as weighted doubles w_k * p_k
+        // uint8 rows: the pivots' main-class words in registers, the non-zero positions of their tails in the sub-lists
         unsigned pm_h[QM], pm_l[QM];
-        double pw_h[QT][4], pw_l[QT][4];
+        int lcnt = 0;                                           // length of the sub-list this lane walks
         int nm_h = 0, nm_l = 0;
         if constexpr (IS_U8) {
-          if (!use_cache) {
+          // pivots are needed for an X pass, and for K12 of a cached iteration whose row i_low lives on another GPU (row sharding:
+          // X is replicated, so K12 is formed here the way that GPU formed it)
+          const bool local_low = i_low >= a.row_begin && i_low < a.row_end;
+          if (!use_cache || (!gain && !local_low)) {
             const unsigned *xh = reinterpret_cast<const unsigned *>(Xb + (size_t)i_high * row_bytes);
             const unsigned *xl = reinterpret_cast<const unsigned *>(Xb + (size_t)piv_l * row_bytes);
-            unsigned th[QT], tl[QT];
 #pragma unroll
             for (int i = 0; i < QM; ++i) {
                 const int w = i * 32 + lane;
                 pm_h[i] = w < a.mw ? __ldg(xh + w) : 0u;
                 pm_l[i] = w < a.mw ? __ldg(xl + w) : 0u;
             }
-#pragma unroll
-            for (int i = 0; i < QT; ++i) {
-                const int w = i * 32 + lane;
-                th[i] = w < a.tw ? __ldg(xh + a.mw + w) : 0u;
-                tl[i] = w < a.tw ? __ldg(xl + a.mw + w) : 0u;
-            }
             nm_h = a.nmain[i_high]; nm_l = a.nmain[piv_l];
             n_h = a.ntail[i_high]; n_l = a.ntail[piv_l];
+            lcnt = u8_build_lists(xh + a.mw, xl + a.mw, sh_wt, lists, lane);
             SVM_STAMP(15);
             int dot = 0;
 #pragma unroll
             for (int i = 0; i < QM; ++i) dot = __dp4a(pm_l[i], pm_h[i], (unsigned)dot);
             dot = __reduce_add_sync(FULL, dot);
-            double acc = 0.0;
-#pragma unroll
-            for (int i = 0; i < QT; ++i) {
-                const int w = min(i * 32 + lane, max(a.tw - 1, 0));
-                const bool valid = i * 32 + lane < a.tw;                     // padding words carry zero weights
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const double wk = valid ? sh_wt[4 * w + c] : 0.0;
-                    pw_h[i][c] = wk * u8_to_f64(th[i], c);
-                    pw_l[i][c] = wk * u8_to_f64(tl[i], c);
-                    if (valid) acc = fma(u8_to_f64(tl[i], c), pw_h[i][c], acc);      // row = x_low, pivot = x_high
-                }
-            }
-            acc = warp_sum_butterfly(acc);
+            double dh, dl;
+            u8_tail_dots(lists.xlt, lcnt, lists, lane, dh, dl);             // row = x_low, pivot = x_high
             const int S = nm_l + nm_h - 2 * dot;
-            double tail = (n_l + n_h) - 2.0 * acc;
+            double tail = (n_l + n_h) - 2.0 * dh;
             if (tail < 0.0) tail = 0.0;
             K12 = svm_exp(-a.gamma * fma((double)S, a.wR, tail));
           } else if (gain) {
             K12 = 1.0;                                          // not used: a gain pass makes no step
-          } else if (i_low >= a.row_begin && i_low < a.row_end) {
+          } else {
             __threadfence();
             K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
-          } else {
-            K12 = u8_kernel_value<QM, QT>(Xb, row_bytes, a.mw, a.tw, sh_wt, a.wR, a.nmain, a.ntail, i_low, i_high, a.gamma, lane);
           }
         } else
         if (!use_cache) {
@@ -998,8 +1007,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
               // ---------------- uint8 rows: a warp per group of eight rows ----------------
               // both sections of a row are padded with zero bytes to whole 128-byte slots (32 lanes x one word), so a lane's
               // words sit at constant offsets from one address per row and need no bounds test
-              const int qm = a.mw >> 5, qt = a.tw >> 5;                        // slots really in use (warp-uniform)
+              const int qm = a.mw >> 5;                                        // slots really in use (warp-uniform)
               const int tail_off = a.mw * 4;
+              SVM_PH_DECL;
               for (int base = 0; base < m; base += 32) {
                 const int cnt = min(32, m - base);
                 const long long j = w0 + base + lane;
@@ -1010,60 +1020,42 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 int my_sh = 0, my_sl = 0;                  // the integer dot products of this lane's row of the block
                 for (int t = 0; t < cnt; t += RPS) {
                     const int rows_here = min(RPS, cnt - t);
+                    SVM_PH(5);
                     mbar_wait(&my_bars[cslot], cphase);
+                    SVM_PH(0);
                     const unsigned char *grp = my_slots + (size_t)cslot * RPS * row_bytes;
                     int SI[2 * RPS];                       // [pivot * RPS + row] integer dot products over the main class
-                    double P[2 * RPS];                     // the same for the weighted tail
 #pragma unroll
-                    for (int k = 0; k < 2 * RPS; ++k) { SI[k] = 0; P[k] = 0.0; }
-                    // eight rows side by side (sixteen independent sums), or four when the group is the short one that ends the
-                    // warp's range: rows beyond the group's last hold bytes of an earlier group, their sums are never read
+                    for (int k = 0; k < 2 * RPS; ++k) SI[k] = 0;
+                    // main class: eight rows side by side (sixteen independent sums), or four when the group is the short one that
+                    // ends the warp's range: rows beyond the group's last hold bytes of an earlier group, their sums are never read
                     const unsigned char *lanep = grp + lane * 4;
-                    if (rows_here > 4) u8_group_sums<QM, QT, RPS, 8>(lanep, row_bytes, tail_off, qm, qt, pm_h, pm_l, pw_h, pw_l, SI, P);
-                    else u8_group_sums<QM, QT, RPS, 4>(lanep, row_bytes, tail_off, qm, qt, pm_h, pm_l, pw_h, pw_l, SI, P);
+                    if (rows_here > 4) u8_main_sums<QM, RPS, 8>(lanep, row_bytes, qm, pm_h, pm_l, SI);
+                    else u8_main_sums<QM, RPS, 4>(lanep, row_bytes, qm, pm_h, pm_l, SI);
+                    SVM_PH(1);
+                    // tail: four lanes per row walk the sub-lists of the pivots' non-zero positions
+                    {
+                        const int r = lane >> 2;
+                        double dh, dl;
+                        u8_tail_dots(grp + (size_t)r * row_bytes + tail_off, r < rows_here ? lcnt : 0, lists, lane, dh, dl);
+                        if (!(lane & 3) && r < rows_here) stage[t + r] = make_double2(dh, dl);
+                    }
+                    SVM_PH(2);
                     __syncwarp();
                     fence_proxy_async();
                     issue_into(cslot);
                     if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
-                    // halving exchanges over the 16 sums (integers and doubles alike): offset 16 splits by pivot, 8 / 4 / 2 by row,
-                    // offset 1 adds; a lane ends with the warp sum for pivot lane >> 4 and row (lane >> 1) & 7.  The doubles are
-                    // added in xor-butterfly order (same bits in every lane of the plain butterfly).
-                    double v1;
-                    {
-                        double v8[8], v4[4], v2[2];
-                        {
-                            const bool up = (lane & 16) != 0;
-#pragma unroll
-                            for (int k = 0; k < 8; ++k) v8[k] = (up ? P[8 + k] : P[k]) + __shfl_xor_sync(FULL, up ? P[k] : P[8 + k], 16);
-                        }
-                        {
-                            const bool up = (lane & 8) != 0;
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) v4[k] = (up ? v8[4 + k] : v8[k]) + __shfl_xor_sync(FULL, up ? v8[k] : v8[4 + k], 8);
-                        }
-                        {
-                            const bool up = (lane & 4) != 0;
-#pragma unroll
-                            for (int k = 0; k < 2; ++k) v2[k] = (up ? v4[2 + k] : v4[k]) + __shfl_xor_sync(FULL, up ? v4[k] : v4[2 + k], 4);
-                        }
-                        {
-                            const bool up = (lane & 2) != 0;
-                            v1 = (up ? v2[1] : v2[0]) + __shfl_xor_sync(FULL, up ? v2[0] : v2[1], 2);
-                        }
-                        v1 = v1 + __shfl_xor_sync(FULL, v1, 1);
-                    }
-                    {
-                        const int r = (lane >> 1) & 7;
-                        if (!(lane & 1) && r < rows_here) *(reinterpret_cast<double *>(&stage[t + r]) + (lane >> 4)) = v1;
-                    }
+                    SVM_PH(3);
                     // the integer sums are exact in any order: the hardware warp reduction, the row's own lane keeps the result
 #pragma unroll
                     for (int r = 0; r < RPS; ++r) {
                         const int sh_ = __reduce_add_sync(FULL, SI[r]), sl_ = __reduce_add_sync(FULL, SI[RPS + r]);
                         if (lane == t + r) { my_sh = sh_; my_sl = sl_; }
                     }
+                    SVM_PH(4);
                 }
                 __syncwarp();
+                SVM_PH(5);
                 if (lane < cnt) {
                     const double2 dd = stage[lane];
                     const int2 ii = make_int2(my_sh, my_sl);
@@ -1075,7 +1067,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     finish_row(a, it, j, fj, aj, yj, qj, kh, kl, acc_best);
                 }
                 __syncwarp();                                  // the parked sums have been read: the next block may overwrite them
+                SVM_PH(6);
               }
+              SVM_PH_FLUSH;
             } else if constexpr (RPS > 1) {
               constexpr bool NEUTRAL_PAD = sizeof(XT) == 4;   // fp32 rows form dot products: an element times a zero pivot register adds +-0.
                                                               // FP64 rows form squared differences: elements beyond the row must be skipped
@@ -1279,7 +1273,8 @@ inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_ste
 {
     return (size_t)warps * kslots * rows_per_step * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128 +
            (size_t)warps * 32 * (sizeof(double2) + sizeof(int2)) +   // + the parked sums of the rows-in-groups passes
-           (size_t)tail_words * 4 * sizeof(double);                  // + the tail weights (uint8 rows)
+           (size_t)tail_words * 4 * (sizeof(double) + sizeof(double2) + sizeof(unsigned short) + 1) + 16;   // + the tail weights and the
+                                                                     //   sub-lists of the pivots' non-zero tail positions (uint8 rows)
 }
 
 } // namespace svm

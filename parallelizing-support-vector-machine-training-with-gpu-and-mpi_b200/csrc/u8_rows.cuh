@@ -27,35 +27,39 @@ __global__ void u8_pack_kernel(const unsigned char *__restrict__ src, long long 
     }
 }
 
-// per-row norms: the integer squared norm over the main class and the weighted norm N(u) = D(u, u) over the tail, formed
-// by a warp exactly as the solver forms D(u, p) (lane l owns the words l, l + 32, ...; bytes in order; butterfly)
-template <int QM, int QT>
+// K-independent pieces of the uint8 arithmetic for one (row, pivot) pair, by ONE thread straight from global memory:
+// the integer dot product over the main class and D(row, pivot) over the tail in the solver's order -- (D_0 + D_1) +
+// (D_2 + D_3), D_c over the words w = c (mod 4) ascending (a zero byte of either row adds +0, so the dense walk here and
+// the solver's walk over the pivots' non-zero positions give the same bits).
+__device__ __forceinline__ void u8_pair_sums(const unsigned char *__restrict__ X, int row_bytes, int mw, int tw, const double *__restrict__ wt,
+                                             long long row, long long piv, int &dot, double &D)
+{
+    const unsigned *xr = reinterpret_cast<const unsigned *>(X + (size_t)row * row_bytes);
+    const unsigned *xp = reinterpret_cast<const unsigned *>(X + (size_t)piv * row_bytes);
+    int s = 0;
+    for (int w = 0; w < mw; ++w) s = (int)__dp4a(__ldg(xr + w), __ldg(xp + w), (unsigned)s);
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int w = 0; w < tw; ++w) {
+        const unsigned ur = __ldg(xr + mw + w), up = __ldg(xp + mw + w);
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            acc[w & 3] = fma((double)((ur >> (8 * c)) & 255u), wt[4 * w + c] * (double)((up >> (8 * c)) & 255u), acc[w & 3]);
+    }
+    dot = s;
+    D = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+// per-row norms: the integer squared norm over the main class and the weighted norm N(u) = D(u, u) over the tail
 __global__ void u8_norms_kernel(const unsigned char *__restrict__ X, long long n, int row_bytes, int mw, int tw, const double *__restrict__ wt,
                                 int *__restrict__ nmain, double *__restrict__ ntail)
 {
-    const int lane = threadIdx.x & 31;
-    const long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
-    const unsigned *x = reinterpret_cast<const unsigned *>(X + (size_t)j * row_bytes);
-    int dot = 0;
-#pragma unroll
-    for (int i = 0; i < QM; ++i) {
-        const int w = i * 32 + lane;
-        if (w < mw) { const unsigned v = __ldg(x + w); dot = (int)__dp4a(v, v, (unsigned)dot); }
-    }
-    dot = __reduce_add_sync(FULL, dot);
-    double acc = 0.0;
-#pragma unroll
-    for (int i = 0; i < QT; ++i) {
-        const int w = i * 32 + lane;
-        if (w < tw) {
-            const unsigned v = __ldg(x + mw + w);
-#pragma unroll
-            for (int c = 0; c < 4; ++c) { const double ud = u8_to_f64(v, c); acc = fma(ud, wt[4 * w + c] * ud, acc); }
-        }
-    }
-    acc = warp_sum_butterfly(acc);
-    if (lane == 0) { nmain[j] = dot; ntail[j] = acc; }
+    int dot;
+    double D;
+    u8_pair_sums(X, row_bytes, mw, tw, wt, j, j, dot, D);
+    nmain[j] = dot;
+    ntail[j] = D;
 }
 
 // scaled FP64 copies of chosen rows (ids == nullptr: rows 0 .. count-1) in the layout of the FP64-row kernels
@@ -85,17 +89,20 @@ __global__ void u8_gather_scale_kernel(const unsigned char *__restrict__ X, int 
     }
 }
 
-// introspection: one kernel row K(., pivot) exactly as the solver forms it (a warp per row)
-template <int QM, int QT>
+// introspection: one kernel row K(., pivot) exactly as the solver forms it (a thread per row)
 __global__ void u8_kernel_row_kernel(const unsigned char *__restrict__ X, long long n, int row_bytes, int mw, int tw, const double *__restrict__ wt,
                                      double wR, const int *__restrict__ nmain, const double *__restrict__ ntail, long long pivot, double gamma,
                                      double *__restrict__ out)
 {
-    const int lane = threadIdx.x & 31;
-    const long long j = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
-    const double k = u8_kernel_value<QM, QT>(X, row_bytes, mw, tw, wt, wR, nmain, ntail, j, pivot, gamma, lane);
-    if (lane == 0) out[j] = k;
+    int dot;
+    double D;
+    u8_pair_sums(X, row_bytes, mw, tw, wt, j, pivot, dot, D);
+    const int S = nmain[j] + nmain[pivot] - 2 * dot;
+    double tail = (ntail[j] + ntail[pivot]) - 2.0 * D;
+    if (tail < 0.0) tail = 0.0;
+    out[j] = svm_exp(-gamma * fma((double)S, wR, tail));
 }
 
 } // namespace svm
