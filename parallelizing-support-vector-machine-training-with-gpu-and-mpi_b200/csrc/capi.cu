@@ -838,9 +838,6 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const int QDEC = q_for_pitch(ctx->dec_pitch4, ctx->dec_f64);      // the decision kernels' row class (warm start)
     // fp32 rows: 8 warps taking rows in groups (SMO_DEFAULT_THREADS); FP64 rows: the same for the longest rows (Q = 13), else 12 warps, a row per step
     int threads = u8 ? SMO_U8_THREADS : ctx->x_f64 ? (Q == 13 ? 256 : 384) : SMO_DEFAULT_THREADS;
-#ifdef SVM_TIMING
-    if (u8 && getenv("SVMB200_U8_THREADS")) { const int t = atoi(getenv("SVMB200_U8_THREADS")); threads = (t == 384 || t == 512) ? t : 256; }
-#endif
 #ifdef SVM_TIMING      // measurement knobs exist in the profiling build only (libsvmb200_timing.so): the product reads no environment
     if (ctx->x_f64 && Q == 13 && getenv("SVMB200_F64_ONE_ROW")) threads = 384;
     if (!ctx->x_f64)
@@ -857,8 +854,11 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
 #ifdef SVM_TIMING
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
 #endif
-    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw) > (size_t)ctx->max_smem_optin) --kslots;
-    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw);
+    // uint8 rows: a per-warp buffer keeps the tails of a 32-row block (walked a lane per row) when it fits beside a ring of two groups
+    int tail_pitch = (u8 && tailw > 0) ? 4 * tailw + 16 : 0;
+    if (tail_pitch && smo_smem_bytes(ctx->pitch4, 2, warps, rps, tailw, tail_pitch) > (size_t)ctx->max_smem_optin) tail_pitch = 0;
+    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw, tail_pitch) > (size_t)ctx->max_smem_optin) --kslots;
+    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw, tail_pitch);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
     const long long n_own = n * (ctx->shard_rank + 1) / ctx->shard_world - n * ctx->shard_rank / ctx->shard_world;
     int grid = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS), (n_own + 7) / 8));
@@ -938,6 +938,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     SmoArgs a{};
     a.X = ctx->X; a.sqn = (ctx->x_f64 || u8) ? nullptr : ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
     a.nmain = ctx->u8_nmain; a.ntail = ctx->u8_ntail; a.wt = ctx->u8_wt; a.mw = ctx->u8_mw; a.tw = ctx->u8_tw; a.wR = ctx->u8_wR;
+    a.tail_pitch = tail_pitch;
     a.cacheq = cache_cap > 0 ? ctx->cacheq : nullptr;
     a.cacheK = ctx->cacheK; a.rec = ctx->rec;
     a.abort_word = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * SMO_MAX_RECS * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
@@ -990,13 +991,14 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     auto launch = [&](int cl) -> cudaError_t {
-#ifdef SVM_TIMING
-        if (u8 && threads == 384)
-            return launch_persistent(smo_persistent_kernel<unsigned char, 8, 1, 384>, a, grid, 384, cl, smem, ctx->stream);
-        if (u8 && threads == 512)
-            return launch_persistent(smo_persistent_kernel<unsigned char, 8, 1, 512>, a, grid, 512, cl, smem, ctx->stream);
-#endif
-        if (u8) return launch_persistent(smo_persistent_kernel<unsigned char, 8, 1, SMO_U8_THREADS>, a, grid, SMO_U8_THREADS, cl, smem, ctx->stream);
+        if (u8) {               // instantiated on the exact number of 128-byte slots of the main class
+            switch (ctx->u8_mw / 32) {
+#define SVM_U8_CASE(S) case S: return launch_persistent(smo_persistent_kernel<unsigned char, S, 1, SMO_U8_THREADS>, a, grid, SMO_U8_THREADS, cl, smem, ctx->stream);
+                SVM_U8_CASE(0) SVM_U8_CASE(1) SVM_U8_CASE(2) SVM_U8_CASE(3) SVM_U8_CASE(4) SVM_U8_CASE(5) SVM_U8_CASE(6) SVM_U8_CASE(7)
+                default: SVM_U8_CASE(8)
+#undef SVM_U8_CASE
+            }
+        }
         return launch_smo_any(KernelKey{ctx->x_f64, Q, CH, threads}, a, grid, cl, smem, ctx->stream);
     };
     cudaError_t le = launch(cluster);

@@ -82,6 +82,7 @@ struct SmoArgs {
     const double *wt;                   // [tw * 4] weights (1 / range)^2 of the tail features (0 for padding bytes)
     int mw, tw;                         // 4-byte words of a row in the main class / in the tail, each padded to a multiple of 32
     double wR;                          // weight of the main class
+    int tail_pitch;                     // > 0: bytes per row of the per-warp buffer that keeps a block's tails (4 * tw + 16); 0: no such buffer
     long long *timing;                  // optional [iterations][8] clock64 stamps of CTA 0 (profiling builds only)
     int timing_cap;
 };
@@ -162,10 +163,11 @@ __device__ __forceinline__ void group_dot2(const unsigned char *grp, int row_byt
 // positions where one of the two pivots is non-zero (MNIST's border pixels: a handful out of 233), from four sub-lists
 // (one per c) that every warp builds at the top of the iteration.
 struct U8Lists {
-    double2 *pp;            // [4][tw] weighted pivot bytes {w_k p_high_k, w_k p_low_k}
-    unsigned short *kk;     // [4][tw] tail position k
+    double2 *pp;            // [4][cap] weighted pivot bytes {w_k p_high_k, w_k p_low_k}
+    unsigned short *kk;     // [4][cap] tail position k
     unsigned char *xlt;     // [4 * tw] tail bytes of the low pivot (the "row" of K12)
     int tw;
+    int cap;                // tw + 4: a sub-list holds at most tw entries, followed by four zero-weight ones
 };
 // Every warp calls this with the same arguments and writes the same values (no CTA barrier needed: a warp reads what it
 // wrote itself).  Sub-list c holds the positions of the words w = c (mod 4), i.e. of the lanes l = c (mod 4), in ascending
@@ -177,29 +179,47 @@ __device__ __forceinline__ int u8_build_lists(const unsigned *__restrict__ xh_ta
     const unsigned before = (0x11111111u << c) & ((1u << lane) - 1u);      // lower lanes of this lane's class
     const unsigned cls = 0x11111111u << c;
     int base = 0;                                                          // entries of this class so far
-    for (int w0 = 0; w0 < L.tw; w0 += 32) {
-        const int w = w0 + lane;                                           // tw is a multiple of 32
-        const unsigned th = __ldg(xh_tail + w), tl = __ldg(xl_tail + w);
-        reinterpret_cast<unsigned *>(L.xlt)[w] = tl;
-        int e = c * L.tw + base, total = 0;
-        bool nz[4];
-        unsigned ballot[4];
+    for (int w0 = 0; w0 < L.tw; w0 += 64) {                                // two slots at a time: their four loads travel together
+        const bool two = w0 + 32 < L.tw;                                   // tw is a multiple of 32
+        unsigned thv[2], tlv[2];
+        thv[0] = __ldg(xh_tail + w0 + lane);
+        tlv[0] = __ldg(xl_tail + w0 + lane);
+        thv[1] = two ? __ldg(xh_tail + w0 + 32 + lane) : 0u;
+        tlv[1] = two ? __ldg(xl_tail + w0 + 32 + lane) : 0u;
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            nz[b] = (((th | tl) >> (8 * b)) & 255u) != 0u;
-            ballot[b] = __ballot_sync(FULL, nz[b]);
-            e += __popc(ballot[b] & before);                               // all bytes of the lower lanes come first
-            total += __popc(ballot[b] & cls);
-        }
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            const int w = w0 + 32 * h + lane;
+            const unsigned th = thv[h], tl = tlv[h];
+            reinterpret_cast<unsigned *>(L.xlt)[w] = tl;
+            int e = c * L.cap + base, total = 0;
+            bool nz[4];
 #pragma unroll
-        for (int b = 0; b < 4; ++b)
-            if (nz[b]) {
-                const double wk = sh_wt[4 * w + b];
-                L.kk[e] = (unsigned short)(4 * w + b);
-                L.pp[e] = make_double2(wk * (double)((th >> (8 * b)) & 255u), wk * (double)((tl >> (8 * b)) & 255u));
-                ++e;
+            for (int b = 0; b < 4; ++b) {
+                nz[b] = (((th | tl) >> (8 * b)) & 255u) != 0u;
+                const unsigned ballot = __ballot_sync(FULL, nz[b]);
+                e += __popc(ballot & before);                              // all bytes of the lower lanes come first
+                total += __popc(ballot & cls);
             }
-        base += total;
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+                if (nz[b]) {
+                    const double wk = sh_wt[4 * w + b];
+                    L.kk[e] = (unsigned short)(4 * w + b);
+                    L.pp[e] = make_double2(wk * (double)((th >> (8 * b)) & 255u), wk * (double)((tl >> (8 * b)) & 255u));
+                    ++e;
+                }
+            base += total;
+        }
+    }
+    // four zero-weight entries behind every sub-list: the walkers take four entries at a time, the first four without looking
+    // at the length (u * 0 adds +0)
+    if (lane < 16) {
+        const int cc = lane & 3;                                           // lanes 0..15: class cc, pad entry lane >> 2
+        const int n_cc = __shfl_sync(0xffffu, base, cc);
+        const int e = cc * L.cap + n_cc + (lane >> 2);
+        L.kk[e] = 0;
+        L.pp[e] = make_double2(0.0, 0.0);
     }
     __syncwarp();
     return base;
@@ -207,42 +227,48 @@ __device__ __forceinline__ int u8_build_lists(const unsigned *__restrict__ xh_ta
 // D(row, pivots) for the row whose tail bytes start at `rowtail` (shared memory): the lane walks sub-list c = lane & 3
 // (`n` entries), the four lanes of a row then form (D_0 + D_1) + (D_2 + D_3).  Whole warp; n = 0 for a lane whose row does
 // not exist.
+// four entries of a sub-list against one row: independent loads first, then the two fma chains (entry order kept)
+__device__ __forceinline__ void u8_walk4(const unsigned char *rowtail, const double2 *pp, const unsigned short *kk, int e, double &ah, double &al)
+{
+    const uint2 k4 = *reinterpret_cast<const uint2 *>(kk + e);             // e is a multiple of 4: 8-byte aligned
+    const double2 p0 = pp[e], p1 = pp[e + 1], p2 = pp[e + 2], p3 = pp[e + 3];
+    const double u0 = (double)rowtail[k4.x & 0xffffu], u1 = (double)rowtail[k4.x >> 16];
+    const double u2 = (double)rowtail[k4.y & 0xffffu], u3 = (double)rowtail[k4.y >> 16];
+    ah = fma(u0, p0.x, ah); al = fma(u0, p0.y, al);
+    ah = fma(u1, p1.x, ah); al = fma(u1, p1.y, al);
+    ah = fma(u2, p2.x, ah); al = fma(u2, p2.y, al);
+    ah = fma(u3, p3.x, ah); al = fma(u3, p3.y, al);
+}
 __device__ __forceinline__ void u8_tail_dots(const unsigned char *rowtail, int n, const U8Lists &L, int lane, double &dh, double &dl)
 {
     const int c = lane & 3;
-    const double2 *pp = L.pp + c * L.tw;
-    const unsigned short *kk = L.kk + c * L.tw;
+    const double2 *pp = L.pp + c * L.cap;
+    const unsigned short *kk = L.kk + c * L.cap;
     double ah = 0.0, al = 0.0;
-    for (int e = 0; e < n; ++e) {
-        const double ud = (double)rowtail[kk[e]];
-        const double2 p = pp[e];
-        ah = fma(ud, p.x, ah);
-        al = fma(ud, p.y, al);
-    }
+    for (int e = 0; e < n; e += 4) u8_walk4(rowtail, pp, kk, e, ah, al);
     __syncwarp();
     ah = ah + __shfl_xor_sync(FULL, ah, 1);
     al = al + __shfl_xor_sync(FULL, al, 1);
     dh = ah + __shfl_xor_sync(FULL, ah, 2);
     dl = al + __shfl_xor_sync(FULL, al, 2);
 }
-// The lane's partial integer dot products of NR rows of a group against both pivots over the main class: word slot by
-// word slot, the rows side by side.  SI: [pivot * RPS + row].
-template <int QM, int RPS, int NR>
-__device__ __forceinline__ void u8_main_sums(const unsigned char *lanep, int row_bytes, int qm, const unsigned (&pm_h)[QM], const unsigned (&pm_l)[QM],
+// SLOTS = the number of 128-byte slots of the main class (a template parameter of the kernel: no branch between the slots,
+// so the loads of all slots are in flight together).
+template <int QM, int SLOTS, int RPS, int NR>
+__device__ __forceinline__ void u8_main_sums(const unsigned char *lanep, int row_bytes, const unsigned (&pm_h)[QM], const unsigned (&pm_l)[QM],
                                              int (&SI)[2 * RPS])
 {
 #pragma unroll
-    for (int i = 0; i < QM; ++i)
-        if (i < qm) {
-            unsigned w[NR];
+    for (int i = 0; i < SLOTS; ++i) {
+        unsigned w[NR];
 #pragma unroll
-            for (int r = 0; r < NR; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + r * row_bytes + i * 128);
+        for (int r = 0; r < NR; ++r) w[r] = *reinterpret_cast<const unsigned *>(lanep + r * row_bytes + i * 128);
 #pragma unroll
-            for (int r = 0; r < NR; ++r) {
-                SI[r] = (int)__dp4a(w[r], pm_h[i], (unsigned)SI[r]);
-                SI[RPS + r] = (int)__dp4a(w[r], pm_l[i], (unsigned)SI[RPS + r]);
-            }
+        for (int r = 0; r < NR; ++r) {
+            SI[r] = (int)__dp4a(w[r], pm_h[i], (unsigned)SI[r]);
+            SI[RPS + r] = (int)__dp4a(w[r], pm_l[i], (unsigned)SI[RPS + r]);
         }
+    }
 }
 
 // membership tests of calc_i_high / calc_i_low (code/main3.cpp:115,134)
@@ -756,13 +782,19 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     double2 *stage = stage_all + warp * 32;
     // (uint8 rows) per warp: the two integer sums of each of the 32 rows of a block; then the tail weights, shared by the CTA
     constexpr bool IS_U8 = sizeof(XT) == 1;
-    constexpr int QM = IS_U8 ? Q : 1;                             // words per lane of the main class
+    constexpr int QM = IS_U8 ? (Q > 0 ? Q : 1) : 1;               // uint8 rows: Q = 128-byte slots of the main class (0 ... 8), exactly
+    constexpr int MSLOTS = IS_U8 ? Q : 0;
     double *sh_wt = reinterpret_cast<double *>(reinterpret_cast<int2 *>(stage_all + WARPS * 32) + WARPS * 32);
     U8Lists lists;
     lists.tw = a.tw;
+    lists.cap = a.tw + 4;
     lists.pp = reinterpret_cast<double2 *>(sh_wt + a.tw * 4);
-    lists.kk = reinterpret_cast<unsigned short *>(lists.pp + a.tw * 4);
-    lists.xlt = reinterpret_cast<unsigned char *>(lists.kk + a.tw * 4);
+    lists.kk = reinterpret_cast<unsigned short *>(lists.pp + lists.cap * 4);
+    lists.xlt = reinterpret_cast<unsigned char *>(lists.kk + lists.cap * 4);
+    // (uint8 rows, when it fits) per warp: the tail bytes of the 32 rows of a block, set aside group by group so that the
+    // block's rows are walked together, a lane per row; the odd pitch (in 16-byte units) spreads the rows over the banks
+    unsigned char *tailbuf = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(lists.xlt + a.tw * 4) + 15) & ~(uintptr_t)15) +
+                             (size_t)warp * 32 * a.tail_pitch;
     if constexpr (IS_U8)
         for (int k = threadIdx.x; k < a.tw * 4; k += THREADS) sh_wt[k] = a.wt[k];
 
@@ -887,7 +919,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         }
 
         // K12 = K(i_high, i_low)  (main3.cpp:241)
-        Pivots<Vec, Q> pv;
+        Pivots<Vec, (Q > 0 ? Q : 1)> pv;
         double K12, n_h = 0.0, n_l = 0.0;
         // uint8 rows: the pivots' main-class words in registers, the non-zero positions of their tails in the sub-lists
         unsigned pm_h[QM], pm_l[QM];
@@ -901,10 +933,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             const unsigned *xh = reinterpret_cast<const unsigned *>(Xb + (size_t)i_high * row_bytes);
             const unsigned *xl = reinterpret_cast<const unsigned *>(Xb + (size_t)piv_l * row_bytes);
 #pragma unroll
-            for (int i = 0; i < QM; ++i) {
-                const int w = i * 32 + lane;
-                pm_h[i] = w < a.mw ? __ldg(xh + w) : 0u;
-                pm_l[i] = w < a.mw ? __ldg(xl + w) : 0u;
+            for (int i = 0; i < MSLOTS; ++i) {                  // a.mw == 32 * MSLOTS
+                pm_h[i] = __ldg(xh + i * 32 + lane);
+                pm_l[i] = __ldg(xl + i * 32 + lane);
             }
             nm_h = a.nmain[i_high]; nm_l = a.nmain[piv_l];
             n_h = a.ntail[i_high]; n_l = a.ntail[piv_l];
@@ -912,7 +943,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             SVM_STAMP(15);
             int dot = 0;
 #pragma unroll
-            for (int i = 0; i < QM; ++i) dot = __dp4a(pm_l[i], pm_h[i], (unsigned)dot);
+            for (int i = 0; i < MSLOTS; ++i) dot = __dp4a(pm_l[i], pm_h[i], (unsigned)dot);
             dot = __reduce_add_sync(FULL, dot);
             double dh, dl;
             u8_tail_dots(lists.xlt, lcnt, lists, lane, dh, dl);             // row = x_low, pivot = x_high
@@ -1007,8 +1038,9 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
               // ---------------- uint8 rows: a warp per group of eight rows ----------------
               // both sections of a row are padded with zero bytes to whole 128-byte slots (32 lanes x one word), so a lane's
               // words sit at constant offsets from one address per row and need no bounds test
-              const int qm = a.mw >> 5;                                        // slots really in use (warp-uniform)
               const int tail_off = a.mw * 4;
+              const bool tail_block = a.tail_pitch > 0;
+              const int n0 = __shfl_sync(FULL, lcnt, 0), n1 = __shfl_sync(FULL, lcnt, 1), n2 = __shfl_sync(FULL, lcnt, 2), n3 = __shfl_sync(FULL, lcnt, 3);
               SVM_PH_DECL;
               for (int base = 0; base < m; base += 32) {
                 const int cnt = min(32, m - base);
@@ -1030,11 +1062,26 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                     // main class: eight rows side by side (sixteen independent sums), or four when the group is the short one that
                     // ends the warp's range: rows beyond the group's last hold bytes of an earlier group, their sums are never read
                     const unsigned char *lanep = grp + lane * 4;
-                    if (rows_here > 4) u8_main_sums<QM, RPS, 8>(lanep, row_bytes, qm, pm_h, pm_l, SI);
-                    else u8_main_sums<QM, RPS, 4>(lanep, row_bytes, qm, pm_h, pm_l, SI);
+                    if (rows_here > 4) u8_main_sums<QM, MSLOTS, RPS, 8>(lanep, row_bytes, pm_h, pm_l, SI);
+                    else u8_main_sums<QM, MSLOTS, RPS, 4>(lanep, row_bytes, pm_h, pm_l, SI);
                     SVM_PH(1);
-                    // tail: four lanes per row walk the sub-lists of the pivots' non-zero positions
-                    {
+                    if (tail_block) {
+                        // tail: set the group's tail bytes aside (16-byte chunks; the block's rows are walked together below)
+                        // eight lanes per row (128 contiguous bytes: all banks once), rows r and r + 4 (tw is a multiple of 32 words:
+                        // a multiple of 8 chunks per row)
+                        const int chunks = a.tw >> 2;
+                        const int r = lane >> 3, q0 = (lane & 7) * 16;
+                        const unsigned char *src = grp + (size_t)r * row_bytes + tail_off + q0;
+                        unsigned char *dst = tailbuf + (size_t)(t + r) * a.tail_pitch + q0;
+                        for (int q = 0; q < chunks; q += 8) {
+                            uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
+                            if (r < rows_here) v0 = *reinterpret_cast<const uint4 *>(src + q * 16);
+                            if (r + 4 < rows_here) v1 = *reinterpret_cast<const uint4 *>(src + 4 * (size_t)row_bytes + q * 16);
+                            if (r < rows_here) *reinterpret_cast<uint4 *>(dst + q * 16) = v0;
+                            if (r + 4 < rows_here) *reinterpret_cast<uint4 *>(dst + 4 * (size_t)a.tail_pitch + q * 16) = v1;
+                        }
+                    } else {
+                        // tail (too long for the buffer): four lanes per row walk the sub-lists of the pivots' non-zero positions
                         const int r = lane >> 2;
                         double dh, dl;
                         u8_tail_dots(grp + (size_t)r * row_bytes + tail_off, r < rows_here ? lcnt : 0, lists, lane, dh, dl);
@@ -1056,8 +1103,22 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 }
                 __syncwarp();
                 SVM_PH(5);
+                double2 dd;
+                if (tail_block) {
+                    // a lane per row: the four sub-lists one after the other (uniform trip counts, broadcast reads of the entries)
+                    const unsigned char *myrow = tailbuf + (size_t)lane * a.tail_pitch;
+                    double sh_[4] = {0.0, 0.0, 0.0, 0.0}, sl_[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)                     // the first four entries of every sub-list, no branch between them
+                        u8_walk4(myrow, lists.pp + c * lists.cap, lists.kk + c * lists.cap, 0, sh_[c], sl_[c]);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const int n = c == 0 ? n0 : c == 1 ? n1 : c == 2 ? n2 : n3;
+                        for (int e = 4; e < n; e += 4) u8_walk4(myrow, lists.pp + c * lists.cap, lists.kk + c * lists.cap, e, sh_[c], sl_[c]);
+                    }
+                    dd = make_double2((sh_[0] + sh_[1]) + (sh_[2] + sh_[3]), (sl_[0] + sl_[1]) + (sl_[2] + sl_[3]));
+                } else if (lane < cnt) dd = stage[lane];
                 if (lane < cnt) {
-                    const double2 dd = stage[lane];
                     const int2 ii = make_int2(my_sh, my_sl);
                     double t_h = (ntj + n_h) - 2.0 * dd.x, t_l = (ntj + n_l) - 2.0 * dd.y;
                     if (t_h < 0.0) t_h = 0.0;
@@ -1269,12 +1330,13 @@ __global__ void peer_rendezvous_kernel(PeerFlags pf, int rank, int peers, unsign
 }
 
 // kslots: ring depth per warp in slots; a slot holds rows_per_step rows
-inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1, int tail_words = 0)
+inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1, int tail_words = 0, int tail_pitch = 0)
 {
     return (size_t)warps * kslots * rows_per_step * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128 +
            (size_t)warps * 32 * (sizeof(double2) + sizeof(int2)) +   // + the parked sums of the rows-in-groups passes
-           (size_t)tail_words * 4 * (sizeof(double) + sizeof(double2) + sizeof(unsigned short) + 1) + 16;   // + the tail weights and the
+           (size_t)tail_words * 4 * (sizeof(double) + 1) + (size_t)(tail_words + 4) * 4 * (sizeof(double2) + sizeof(unsigned short)) + 32 +  // + the tail weights and the
                                                                      //   sub-lists of the pivots' non-zero tail positions (uint8 rows)
+           (size_t)warps * 32 * tail_pitch;                          // + the blocks' tails set aside
 }
 
 } // namespace svm
