@@ -90,6 +90,7 @@ typedef struct {
     int32_t n_sv;            /* count of alpha > sv_tol */
     int32_t grid_blocks;     /* persistent grid actually launched */
     int32_t launches;        /* kernels launched by this call */
+    int32_t cluster_size;    /* CTAs per thread-block cluster of the persistent grid (2; 1 when the device refused clusters) */
 } svmb200_stats;
 
 void svmb200_default_params(svmb200_params *p);

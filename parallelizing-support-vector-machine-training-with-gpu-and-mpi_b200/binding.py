@@ -30,7 +30,7 @@ class Stats(C.Structure):
     _fields_ = [("num_iter", C.c_int32), ("stop_reason", C.c_int32), ("i_high", C.c_int64), ("i_low", C.c_int64),
                 ("b_high", C.c_double), ("b_low", C.c_double), ("smo_ms", C.c_double), ("init_ms", C.c_double),
                 ("x_passes", C.c_int64), ("cache_hits", C.c_int64), ("x_bytes_streamed", C.c_int64),
-                ("n_sv", C.c_int32), ("grid_blocks", C.c_int32), ("launches", C.c_int32)]
+                ("n_sv", C.c_int32), ("grid_blocks", C.c_int32), ("launches", C.c_int32), ("cluster_size", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -627,6 +627,9 @@ static cudaError_t launch_persistent(K kernel, const SmoArgs &args, int grid, in
     if (cluster > 1) {
         int max_clusters = 0;
         e = cudaOccupancyMaxActiveClusters(&max_clusters, kernel, &cfg);
+#ifdef SVM_TIMING
+        fprintf(stderr, "svmb200: cudaOccupancyMaxActiveClusters -> %d clusters of %d (%s) for a grid of %d\n", max_clusters, cluster, cudaGetErrorString(e), grid);
+#endif
         if (e != cudaSuccess) return e;
         if (max_clusters * cluster < grid) return cudaErrorCooperativeLaunchTooLarge;
     }
@@ -1003,6 +1006,9 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     };
     cudaError_t le = launch(cluster);
     if (le != cudaSuccess && cluster > 1) {      // this device cannot co-schedule the clusters: same kernel, cluster size 1
+#ifdef SVM_TIMING
+        fprintf(stderr, "svmb200: cluster launch refused (%s), falling back to cluster size 1\n", cudaGetErrorString(le));
+#endif
         (void)cudaGetLastError();
         cluster = 1;
         le = launch(cluster);
@@ -1051,6 +1057,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         stats->n_sv = (int)ctx->sv_ids.size();
         stats->grid_blocks = grid;
         stats->launches = ctx->launches - launches0;
+        stats->cluster_size = ctx->cluster_size;
     }
     return SVMB200_OK;
 }
