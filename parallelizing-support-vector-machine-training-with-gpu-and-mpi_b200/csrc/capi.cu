@@ -63,7 +63,7 @@ struct svmb200_ctx {
     bool dec_f64 = false;
     int dec_pitch4 = 0;
     // uint8 storage: layout of a packed row and its per-row norms (smo_kernel.cuh "uint8 rows")
-    int u8_mw = 0, u8_tw = 0, u8_R = 0, u8_M = 0, u8_T = 0;
+    int u8_mw = 0, u8_tw = 0, u8_tail_pitch = 0, u8_R = 0, u8_M = 0, u8_T = 0;
     double u8_wR = 0.0;
     int *u8_nmain = nullptr, *u8_pos = nullptr, *u8_src = nullptr;
     double *u8_ntail = nullptr, *u8_wt = nullptr;
@@ -85,7 +85,7 @@ struct svmb200_ctx {
     int cache_valid_cap = 0, cache_valid_chunk = 0;
     double cache_valid_gamma = 0.0;
     long long cache_counter = 0;
-    Rec *rec = nullptr;                  // [2][SMO_MAX_RECS] exchange records + the abort word
+    Rec *rec = nullptr;                  // [2][SMO_REC_COPIES][SMO_MAX_RECS] exchange records + the abort word
     SmoResult *result = nullptr;
     int *trace = nullptr;
     int trace_alloc = 0, trace_count = 0;
@@ -381,8 +381,10 @@ static int pack_u8_rows(svmb200_ctx *ctx, const unsigned char *raw, long long n)
     const int M = (int)main_idx.size(), T = (int)tail_idx.size();
     // both sections are padded with zero bytes (zero weights) to whole 128-byte slots: 32 lanes x one 4-byte word
     const int mw = ((M + 3) / 4 + 31) & ~31, tw = ((T + 3) / 4 + 31) & ~31;
-    const int row_bytes = std::max(128, 4 * (mw + tw));
-    std::vector<int> src(row_bytes, -1), pos(d, -1);
+    // two arrays (u8_rows.cuh: U8View): [n][4 * mw] bytes of the main class, then [n][tail_pitch] bytes of the tail
+    const int tail_pitch = tw ? 4 * tw + 16 : 0;
+    const int row_bytes = 4 * mw + tail_pitch;
+    std::vector<int> src(std::max(row_bytes, 4), -1), pos(d, -1);
     std::vector<double> wt((size_t)std::max(tw, 1) * 4, 0.0);
     for (int k = 0; k < M; ++k) { src[k] = main_idx[k]; pos[main_idx[k]] = k; }
     for (int k = 0; k < T; ++k) {
@@ -392,22 +394,24 @@ static int pack_u8_rows(svmb200_ctx *ctx, const unsigned char *raw, long long n)
         wt[k] = sk * sk;
     }
     const double sR = R ? 1.0 / (double)R : 0.0;
-    ctx->u8_R = R; ctx->u8_M = M; ctx->u8_T = T; ctx->u8_mw = mw; ctx->u8_tw = tw; ctx->u8_wR = sR * sR;
-    ctx->pitch4 = row_bytes / 16;
+    ctx->u8_R = R; ctx->u8_M = M; ctx->u8_T = T; ctx->u8_mw = mw; ctx->u8_tw = tw; ctx->u8_tail_pitch = tail_pitch; ctx->u8_wR = sR * sR;
+    ctx->pitch4 = row_bytes / 16;                   // bytes of a row over both arrays (accounting only)
     if (dev_free(ctx, ctx->u8_src) || dev_free(ctx, ctx->u8_pos) || dev_free(ctx, ctx->u8_wt) || dev_free(ctx, ctx->X)) return SVMB200_ECUDA;
     CK(cudaMalloc(&ctx->u8_src, src.size() * sizeof(int)));
     CK(cudaMalloc(&ctx->u8_pos, pos.size() * sizeof(int)));
     CK(cudaMalloc(&ctx->u8_wt, wt.size() * sizeof(double)));
-    CK(cudaMalloc(&ctx->X, (size_t)n * row_bytes));
+    CK(cudaMalloc(&ctx->X, std::max<size_t>((size_t)n * row_bytes, 256)));
     CK(cudaMemcpyAsync(ctx->u8_src, src.data(), src.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->u8_pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->u8_wt, wt.data(), wt.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     const long long words = n * (row_bytes / 4);
-    u8_pack_kernel<<<(int)std::min<long long>((words + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
-        raw, n, d, row_bytes, ctx->u8_src, static_cast<unsigned char *>(ctx->X));
-    CK(cudaGetLastError());
-    u8_norms_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(static_cast<const unsigned char *>(ctx->X), n, row_bytes, mw, tw, ctx->u8_wt,
-                                                                             ctx->u8_nmain, ctx->u8_ntail);
+    if (words > 0) {
+        u8_pack_kernel<<<(int)std::min<long long>((words + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
+            raw, n, d, mw, tail_pitch, ctx->u8_src, static_cast<unsigned char *>(ctx->X));
+        CK(cudaGetLastError());
+    }
+    u8_norms_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(U8View(ctx->X, n, mw, tail_pitch), n, mw, tw, ctx->u8_wt, ctx->u8_nmain,
+                                                                             ctx->u8_ntail);
     CK(cudaGetLastError());
     ctx->launches += 2;
     CK(cudaStreamSynchronize(ctx->stream));      // src / pos / wt are host temporaries
@@ -807,7 +811,7 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
     const long long total = (long long)nsv * ctx->dec_pitch4;
     const int gblocks = (int)std::min<long long>((total + 255) / 256, ctx->num_sms * 16);
     if (ctx->x_u8) {            // the support vectors' bytes become scaled FP64 rows
-        u8_gather_scale_kernel<<<gblocks, 256, 0, ctx->stream>>>(static_cast<const unsigned char *>(ctx->X), ctx->pitch4 * 16, ctx->u8_pos, ctx->minv,
+        u8_gather_scale_kernel<<<gblocks, 256, 0, ctx->stream>>>(U8View(ctx->X, ctx->n, ctx->u8_mw, ctx->u8_tail_pitch), ctx->u8_pos, ctx->minv,
                                                                    ctx->maxv, ctx->d, static_cast<const int *>(ctx->scratch), nsv, ctx->dec_pitch4,
                                                                    static_cast<double *>(ctx->svX));
         CK(cudaMemsetAsync(ctx->svn, 0, (size_t)nsv * sizeof(double), ctx->stream));
@@ -853,15 +857,18 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const int rps = u8 ? 8 : !ctx->x_f64 ? (threads <= 256 ? (Q == 8 ? 2 : 4) : 1) : (Q == 13 && threads == 256) ? 2 : 1;   // = smo_rows_per_step<XT, Q, THREADS>()
     const int tailw = u8 ? ctx->u8_tw : 0;
     // ring depth: as many groups as fit, at most 4 (two at the MNIST shape: one in use, one in flight); a row per step: 4 rows at Q = 7, else 2
-    int kslots = rps > 1 ? 4 : (Q == 7 && !ctx->x_f64) ? 4 : 2;
+    int kslots = u8 ? 3 : rps > 1 ? 4 : (Q == 7 && !ctx->x_f64) ? 4 : 2;          // uint8 rows: groups of the main class only, three deep
 #ifdef SVM_TIMING
     if (const char *e = getenv("SVMB200_KSLOTS")) kslots = std::max(2, std::min(SMO_KSLOTS_MAX, atoi(e)));
 #endif
-    // uint8 rows: a per-warp buffer keeps the tails of a 32-row block (walked a lane per row) when it fits beside a ring of two groups
-    int tail_pitch = (u8 && tailw > 0) ? 4 * tailw + 16 : 0;
-    if (tail_pitch && smo_smem_bytes(ctx->pitch4, 2, warps, rps, tailw, tail_pitch) > (size_t)ctx->max_smem_optin) tail_pitch = 0;
-    while (kslots > 2 && smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw, tail_pitch) > (size_t)ctx->max_smem_optin) --kslots;
-    const size_t smem = smo_smem_bytes(ctx->pitch4, kslots, warps, rps, tailw, tail_pitch);
+    // uint8 rows: the ring carries the main class; a per-warp buffer receives the tails of a block of 32 rows (walked a lane per
+    // row), of 16 or 8 rows when 32 do not fit beside a ring of two groups
+    const int ring_pitch4 = u8 ? ctx->u8_mw / 4 : ctx->pitch4;
+    const int tail_pitch = u8 ? ctx->u8_tail_pitch : 0;
+    int tail_rows = 32;
+    while (tail_rows > 8 && smo_smem_bytes(ring_pitch4, 2, warps, rps, tailw, tail_pitch, tail_rows) > (size_t)ctx->max_smem_optin) tail_rows /= 2;
+    while (kslots > 2 && smo_smem_bytes(ring_pitch4, kslots, warps, rps, tailw, tail_pitch, tail_rows) > (size_t)ctx->max_smem_optin) --kslots;
+    const size_t smem = smo_smem_bytes(ring_pitch4, kslots, warps, rps, tailw, tail_pitch, tail_rows);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
     const long long n_own = n * (ctx->shard_rank + 1) / ctx->shard_world - n * ctx->shard_rank / ctx->shard_world;
     int grid = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS), (n_own + 7) / 8));
@@ -886,7 +893,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         ctx->cacheK_elems = (size_t)cache_cap * n;
     }
 
-    const size_t rec_bytes = (size_t)2 * SMO_MAX_RECS * sizeof(Rec) + 256;     // two generations of records + the abort word
+    const size_t rec_bytes = (size_t)2 * SMO_REC_COPIES * SMO_MAX_RECS * sizeof(Rec) + 256;     // two generations of records (in copies) + the abort word
     if (!ctx->rec) CK(cudaMalloc(&ctx->rec, rec_bytes));
     const int trace_cap = std::max(0, params->trace_cap);
     if (trace_cap > ctx->trace_alloc) {
@@ -921,8 +928,8 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
             if (!ctx->xdec_valid) {
                 const long long total = n * ctx->dec_pitch4;
                 u8_gather_scale_kernel<<<(int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
-                    static_cast<const unsigned char *>(ctx->X), ctx->pitch4 * 16, ctx->u8_pos, ctx->minv, ctx->maxv, ctx->d, nullptr, n,
-                    ctx->dec_pitch4, static_cast<double *>(ctx->Xdec));
+                    U8View(ctx->X, n, ctx->u8_mw, ctx->u8_tail_pitch), ctx->u8_pos, ctx->minv, ctx->maxv, ctx->d, nullptr, n, ctx->dec_pitch4,
+                    static_cast<double *>(ctx->Xdec));
                 ctx->launches += 1;
                 CK(cudaGetLastError());
                 ctx->xdec_valid = true;
@@ -941,10 +948,10 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     SmoArgs a{};
     a.X = ctx->X; a.sqn = (ctx->x_f64 || u8) ? nullptr : ctx->sqn; a.y = ctx->y; a.f = ctx->f; a.alpha = ctx->alpha;
     a.nmain = ctx->u8_nmain; a.ntail = ctx->u8_ntail; a.wt = ctx->u8_wt; a.mw = ctx->u8_mw; a.tw = ctx->u8_tw; a.wR = ctx->u8_wR;
-    a.tail_pitch = tail_pitch;
+    a.tail_pitch = tail_pitch; a.tail_rows = tail_rows;
     a.cacheq = cache_cap > 0 ? ctx->cacheq : nullptr;
     a.cacheK = ctx->cacheK; a.rec = ctx->rec;
-    a.abort_word = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * SMO_MAX_RECS * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
+    a.abort_word = reinterpret_cast<unsigned *>(reinterpret_cast<char *>(ctx->rec) + (size_t)2 * SMO_REC_COPIES * SMO_MAX_RECS * sizeof(Rec) + 128); a.trace = ctx->trace; a.result = ctx->result;
     a.n = n; a.pitch4 = ctx->pitch4; a.kslots = kslots; a.cache_cap = cache_cap; a.trace_cap = trace_cap;
     a.max_iter = params->max_iter;
     a.wss = params->wss;
@@ -970,6 +977,14 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     a.row_begin = n * ctx->shard_rank / ctx->shard_world;
     a.row_end = n * (ctx->shard_rank + 1) / ctx->shard_world;
     a.mailbox = ctx->mailbox;
+    a.mailbox_copies = 1;
+    for (int r = 0, first = 1; r < ctx->shard_world; ++r) {       // the clusters of the smallest grid among the GPUs (same rule as `grid` above)
+        const long long own_r = n * (r + 1) / ctx->shard_world - n * r / ctx->shard_world;
+        int g = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS), (own_r + 7) / 8));
+        if (g >= 2) g /= 2;                                        // clusters of two (a launch that falls back to no clusters has more records)
+        a.mailbox_copies = first ? std::min(SMO_MB_COPIES, g) : std::min(a.mailbox_copies, g);
+        first = 0;
+    }
     for (int p = 0; p < 8; ++p) a.peer_mailbox[p] = ctx->peer_mailbox[p];
     a.epoch = ++ctx->shard_epoch;
     a.timing = nullptr; a.timing_cap = 0;
@@ -987,7 +1002,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         // the GPUs of a row-sharded run meet on the device before the timed launch: every process reaches this point at
         // its own time (host skew of a millisecond or more), and the persistent kernels run in lock step once all are there
         PeerFlags pf{};
-        for (int p = 0; p < 8; ++p) pf.peer[p] = ctx->peer_mailbox[p] ? reinterpret_cast<unsigned long long *>(ctx->peer_mailbox[p] + 16) : nullptr;
+        for (int p = 0; p < 8; ++p) pf.peer[p] = ctx->peer_mailbox[p] ? reinterpret_cast<unsigned long long *>(ctx->peer_mailbox[p] + SMO_MB_RECS) : nullptr;
         peer_rendezvous_kernel<<<1, 32, 0, ctx->stream>>>(pf, ctx->shard_rank, ctx->shard_world, (unsigned long long)a.epoch);
         ctx->launches += 1;
         CK(cudaGetLastError());
@@ -1070,8 +1085,8 @@ extern "C" int svmb200_shard_setup(svmb200_ctx *ctx, int32_t rank, int32_t world
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     CK(cudaSetDevice(ctx->device));
     if (ctx->mailbox) FAIL(SVMB200_ESTATE, "svmb200_shard_setup called twice");
-    CK(cudaMalloc(&ctx->mailbox, (size_t)(2 * 8 + 1) * sizeof(Rec)));      // [2][8] records + 8 rendezvous flags
-    CK(cudaMemset(ctx->mailbox, 0, (size_t)(2 * 8 + 1) * sizeof(Rec)));
+    CK(cudaMalloc(&ctx->mailbox, (size_t)(SMO_MB_RECS + 1) * sizeof(Rec)));      // [2][copies][8] records + 8 rendezvous flags
+    CK(cudaMemset(ctx->mailbox, 0, (size_t)(SMO_MB_RECS + 1) * sizeof(Rec)));
     cudaIpcMemHandle_t h;
     CK(cudaIpcGetMemHandle(&h, ctx->mailbox));
     memcpy(handle_out, &h, sizeof h);
@@ -1480,8 +1495,8 @@ int svmb200_kernel_row(svmb200_ctx *ctx, int64_t i, double gamma, int32_t accum_
     cudaError_t e;
     if (ctx->x_u8) {
         u8_kernel_row_kernel<<<(unsigned)((ctx->n + 127) / 128), 128, 0, ctx->stream>>>(
-            static_cast<const unsigned char *>(ctx->X), ctx->n, ctx->pitch4 * 16, ctx->u8_mw, ctx->u8_tw, ctx->u8_wt, ctx->u8_wR, ctx->u8_nmain,
-            ctx->u8_ntail, i, gamma, out);
+            U8View(ctx->X, ctx->n, ctx->u8_mw, ctx->u8_tail_pitch), ctx->n, ctx->u8_mw, ctx->u8_tw, ctx->u8_wt, ctx->u8_wR, ctx->u8_nmain, ctx->u8_ntail,
+            i, gamma, out);
         e = cudaGetLastError();
     } else
         e = launch_krow_any(KernelKey{ctx->x_f64, q_for_pitch(ctx->pitch4, ctx->x_f64), CH, 0}, ctx->X, ctx->x_f64 ? nullptr : ctx->sqn,
@@ -1544,7 +1559,7 @@ int svmb200_get_x_scaled(svmb200_ctx *ctx, float *Xs)
         if (int rc = ensure_work(ctx, 1, bytes)) return rc;
         const long long total = ctx->n * ctx->dec_pitch4;
         u8_gather_scale_kernel<<<(int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
-            static_cast<const unsigned char *>(ctx->X), ctx->pitch4 * 16, ctx->u8_pos, ctx->minv, ctx->maxv, ctx->d, nullptr, ctx->n, ctx->dec_pitch4,
+            U8View(ctx->X, ctx->n, ctx->u8_mw, ctx->u8_tail_pitch), ctx->u8_pos, ctx->minv, ctx->maxv, ctx->d, nullptr, ctx->n, ctx->dec_pitch4,
             static_cast<double *>(ctx->work[1]));
         CK(cudaGetLastError());
         std::vector<double> tmp((size_t)ctx->n * ctx->d);

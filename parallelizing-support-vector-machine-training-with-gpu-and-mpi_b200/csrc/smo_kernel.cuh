@@ -18,9 +18,9 @@
 //        loaded with an evict-last policy and stays in L2 from one pass to the next;
 //        -- or, when both kernel rows are in the HBM row cache, a thread-per-row pass over the two
 //        cached rows instead of X;
-//     3. reduces its candidates, publishes one 128-byte self-validating record, adds 1 to an arrival counter, and
-//        reads all other CTAs' records once the count is complete (an all-gather through L2: the only grid-wide
-//        synchronisation).
+//     3. reduces its candidates inside its thread-block cluster (distributed shared memory), whose leader publishes one
+//        128-byte self-validating record and polls the other clusters' records directly (an all-gather through L2: the
+//        only grid-wide synchronisation; see "the record exchange" below).
 //
 // All mutable state (f, alpha, cache slots, cache bookkeeping) of row j is touched only by the CTA
 // that owns row j, so the record exchange is the only cross-CTA communication.
@@ -73,16 +73,21 @@ struct SmoArgs {
     int peers;                          // GPUs sharing the rows
     int rank;                           // this GPU
     long long row_begin, row_end;       // rows owned by this GPU (X is replicated, state is global-sized)
-    Rec *mailbox;                       // [2][8] local mailbox written by peers
+    Rec *mailbox;                       // [2][SMO_MB_COPIES][8] local mailbox written by peers
+    int mailbox_copies;                 // copies in use: min(SMO_MB_COPIES, clusters of the smallest grid among the GPUs)
     Rec *peer_mailbox[8];               // peers' mailboxes (peer-mapped device pointers; [rank] is the local one)
     int epoch;                          // launch number, folded into the mailbox words so that stale records never match
-    // ---- uint8 rows (storage "u8"): X is [n][pitch4 * 16] bytes = mw words of the main class | tw words of the tail | padding
+    // ---- uint8 rows (storage "u8"): X is two arrays, [n][4 * mw] bytes of the main class, then [n][tail_pitch] bytes of the
+    //      tail (the sections of a row are copied by different bulk copies: the main class in groups of eight rows into the
+    //      ring, the tails of a block of tail_rows rows straight into the buffer they are walked from)
     const int *nmain;                   // [n] integer squared norms over the main class
     const double *ntail;                // [n] weighted squared norms over the tail
     const double *wt;                   // [tw * 4] weights (1 / range)^2 of the tail features (0 for padding bytes)
     int mw, tw;                         // 4-byte words of a row in the main class / in the tail, each padded to a multiple of 32
     double wR;                          // weight of the main class
-    int tail_pitch;                     // > 0: bytes per row of the per-warp buffer that keeps a block's tails (4 * tw + 16); 0: no such buffer
+    int tail_pitch;                     // bytes per row of the tail array and of the per-warp buffer that receives a block of it: 4 * tw + 16
+                                        // (the odd pitch in 16-byte units spreads the rows over the banks); 0 when there is no tail
+    int tail_rows;                      // rows of such a block: 32 (a lane per row of the warp's 32-row block), 16 or 8 when shared memory is short
     long long *timing;                  // optional [iterations][8] clock64 stamps of CTA 0 (profiling builds only)
     int timing_cap;
 };
@@ -450,6 +455,13 @@ __device__ __forceinline__ PairStep pair_update(int y_h, int y_l, double a_h, do
 //   4. cluster: the leader writes the grid's winners into its partner's shared memory and arrives on its mbarrier.
 // With a cluster size of 1 (tiny grids, or a device that cannot co-schedule the clusters) hops 2 and 4 fall away.
 constexpr int REC_WORDS = 16;
+constexpr int SMO_MAX_RECS = 160;         // records per exchange: clusters of the grid (74 on a B200; 148 with a cluster size of 1)
+// Loads that poll one line from many SMs serialise in L2 (measured: +29 ns per further reader of a line and round -- 74 readers
+// of every record cost 2.6 us per exchange, 18 cost 1.0 us).  So every record is stored in SMO_REC_COPIES copies (lines) and
+// leader c polls copy c mod SMO_REC_COPIES: a line then has at most five readers.  The peers' mailboxes likewise.
+constexpr int SMO_REC_COPIES = 16;
+constexpr int SMO_MB_COPIES = 16;                          // copies of a GPU's mailbox
+constexpr int SMO_MB_RECS = 2 * SMO_MB_COPIES * 8;         // [generation][copy][sending GPU]; the rendezvous flags follow
 struct __align__(128) Rec { unsigned long long w[REC_WORDS]; };
 
 // word layout: the two 32-bit halves of one value share a 16-byte pair of words
@@ -498,6 +510,48 @@ __device__ __forceinline__ void rec_store(Rec *r, const LocalBest &b, unsigned s
         if (SYS) asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
         else asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
     }
+}
+// the word pair `pair` (0..7) of a record
+__device__ __forceinline__ void rec_word_pair(const LocalBest &b, int pair, unsigned &d0, unsigned &d1)
+{
+    switch (pair) {
+    case 0: d0 = rec_word(b, 0); d1 = rec_word(b, 1); break;
+    case 1: d0 = rec_word(b, 2); d1 = rec_word(b, 3); break;
+    case 2: d0 = rec_word(b, 4); d1 = rec_word(b, 5); break;
+    case 3: d0 = rec_word(b, 6); d1 = rec_word(b, 7); break;
+    case 4: d0 = rec_word(b, 8); d1 = rec_word(b, 9); break;
+    case 5: d0 = rec_word(b, 10); d1 = rec_word(b, 11); break;
+    case 6: d0 = rec_word(b, 12); d1 = rec_word(b, 13); break;
+    default: d0 = rec_word(b, 14); d1 = rec_word(b, 15); break;
+    }
+}
+// the whole warp publishes record `cid` in all copies, four copies per store instruction: lane l writes the word pair l & 7
+// of the copies l >> 3, 4 + (l >> 3), ...
+__device__ __forceinline__ void rec_store_copies(Rec *recs, int cid, const LocalBest &b, unsigned seq, int lane)
+{
+    static_assert(SMO_REC_COPIES % 4 == 0, "32 lanes = 4 copies x 8 word pairs");
+    unsigned d0, d1;
+    rec_word_pair(b, lane & 7, d0, d1);
+    const unsigned long long v0 = ((unsigned long long)seq << 32) | d0, v1 = ((unsigned long long)seq << 32) | d1;
+#pragma unroll
+    for (int c = lane >> 3; c < SMO_REC_COPIES; c += 4) {
+        Rec *r = recs + (size_t)c * SMO_MAX_RECS + cid;
+        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[2 * (lane & 7)]), "l"(v0), "l"(v1) : "memory");
+    }
+}
+// one copy of this GPU's record into every peer's mailbox (NVLink, system scope): lane l writes the word pair l & 7 for the
+// peers l >> 3 and 4 + (l >> 3)
+__device__ __forceinline__ void mailbox_store(Rec *const (&peer_mailbox)[8], int peers, int rank, int slot, const LocalBest &b, unsigned seq, int lane)
+{
+    unsigned d0, d1;
+    rec_word_pair(b, lane & 7, d0, d1);
+    const unsigned long long v0 = ((unsigned long long)seq << 32) | d0, v1 = ((unsigned long long)seq << 32) | d1;
+#pragma unroll
+    for (int p = lane >> 3; p < 8; p += 4)
+        if (p < peers) {
+            Rec *r = peer_mailbox[p] + slot + rank;
+            asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[2 * (lane & 7)]), "l"(v0), "l"(v1) : "memory");
+        }
 }
 template <bool SYS>
 __device__ __forceinline__ void ld_pair(const unsigned long long *p, unsigned long long &w0, unsigned long long &w1)
@@ -560,7 +614,6 @@ __device__ __forceinline__ void dsmem_put_best(uint32_t addr, const Best &b, uin
     dsmem_st_async2(addr + 16, (unsigned long long)b.q, ((unsigned long long)(unsigned)b.y << 32) | (unsigned)b.idx, bar_addr);
 }
 
-constexpr int SMO_MAX_RECS = 160;         // records per exchange: clusters of the grid (74 on a B200; 148 with a cluster size of 1)
 constexpr int POLL_GROUPS_MAX = 5;        // groups of four records a warp polls: 8 warps x 5 x 4 = 160
 constexpr int REC_STRIDE = REC_WORDS + 1;
 
@@ -594,43 +647,77 @@ constexpr long long PEER_TIMEOUT_CLOCKS = 6000000000LL;   // ~3 s at 1.97 GHz: a
 
 // Poll `count` records starting at `recs` until every word carries `seq`, and stage their data words in shared memory.
 // Called by all warps of a leader CTA; warp w takes the groups of four records w, w + nwarps, ... (8 lanes x 16 bytes
-// cover a record, so a warp's load covers four records in one coalesced request).
+// cover a record, so a warp's load covers four records in one coalesced request).  Two sets of loads are kept in flight
+// half a round trip apart (set B is requested while set A travels, A is looked at, requested again, then B is looked
+// at, ...), so a record is seen at most half a round trip after it could have been; a group that is complete is staged
+// and not asked for again.
 // Returns false if the wait was given up: `abort_word` set by another CTA, or (deadline != 0) the clock ran out, in which
 // case this CTA sets the abort word so that every other wait on this GPU ends too.
-template <bool SYS>
-__device__ __forceinline__ bool poll_records(const Rec *recs, int count, unsigned seq, unsigned (*stage)[REC_STRIDE], unsigned *abort_word,
-                                             long long deadline)
+template <bool SYS, int G, bool STAGGER>
+__device__ __forceinline__ bool poll_records_impl(const Rec *recs, int count, unsigned seq, unsigned (*stage)[REC_STRIDE], unsigned *abort_word,
+                                                  long long deadline)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nwarps = (int)(blockDim.x >> 5);
     const int sub = lane >> 3, pair = lane & 7;
-    unsigned long long w0[POLL_GROUPS_MAX], w1[POLL_GROUPS_MAX];
-    unsigned spins = 0;
-    bool ok_all = true;
-    for (;;) {
-        bool ok = true;
+    unsigned long long a0[G], a1[G], b0[STAGGER ? G : 1], b1[STAGGER ? G : 1];
+    unsigned pending = 0;                                  // warp-uniform: groups of this warp that are not complete yet
 #pragma unroll
-        for (int u = 0; u < POLL_GROUPS_MAX; ++u) {
+    for (int u = 0; u < G; ++u)
+        if ((warp + u * nwarps) * 4 < count) pending |= 1u << u;
+    auto request = [&](auto &x0, auto &x1) {
+#pragma unroll
+        for (int u = 0; u < G; ++u) {
             const int r = (warp + u * nwarps) * 4 + sub;
-            if (r < count) {
-                ld_pair<SYS>(&recs[r].w[2 * pair], w0[u], w1[u]);
-                ok = ok && (unsigned)(w0[u] >> 32) == seq && (unsigned)(w1[u] >> 32) == seq;
+            if (((pending >> u) & 1u) && r < count) ld_pair<SYS>(&recs[r].w[2 * pair], x0[u], x1[u]);
+        }
+    };
+    auto look = [&](const auto &x0, const auto &x1) {
+#pragma unroll
+        for (int u = 0; u < G; ++u)
+            if ((pending >> u) & 1u) {
+                const int r = (warp + u * nwarps) * 4 + sub;
+                const bool ok = r >= count || ((unsigned)(x0[u] >> 32) == seq && (unsigned)(x1[u] >> 32) == seq);
+                if (__all_sync(FULL, ok)) {
+                    if (r < count) { stage[r][2 * pair] = (unsigned)x0[u]; stage[r][2 * pair + 1] = (unsigned)x1[u]; }
+                    pending &= ~(1u << u);
+                }
             }
+    };
+    unsigned spins = 0;
+    if (STAGGER && pending) {
+        request(a0, a1);
+        const long long t0 = clock64();
+        while (clock64() - t0 < 500) { }                  // about half an L2 round trip
+    }
+    while (pending) {
+        if (STAGGER) {
+            request(b0, b1);
+            look(a0, a1);
+            if (!pending) break;
+            request(a0, a1);
+            look(b0, b1);
+        } else {
+            request(a0, a1);
+            look(a0, a1);
         }
-        if (__all_sync(FULL, ok)) break;
-        if ((++spins & 255u) == 0) {
-            if (ld_relaxed_gpu_u32(abort_word)) { ok_all = false; break; }
-            if (deadline && clock64() > deadline) { st_relaxed_gpu_u32(abort_word, 1u); ok_all = false; break; }
+        if ((++spins & 127u) == 0) {
+            if (ld_relaxed_gpu_u32(abort_word)) return false;
+            if (deadline && clock64() > deadline) { st_relaxed_gpu_u32(abort_word, 1u); return false; }
         }
     }
-    if (ok_all) {
-#pragma unroll
-        for (int u = 0; u < POLL_GROUPS_MAX; ++u) {
-            const int r = (warp + u * nwarps) * 4 + sub;
-            if (r < count) { stage[r][2 * pair] = (unsigned)w0[u]; stage[r][2 * pair + 1] = (unsigned)w1[u]; }
-        }
-    }
-    return ok_all;
+    return true;
+}
+template <bool SYS>
+__device__ __forceinline__ bool poll_records(const Rec *recs, int count, unsigned seq, unsigned (*stage)[REC_STRIDE], unsigned *abort_word,
+                                             long long deadline)
+{
+    // up to three groups per warp (clusters of two CTAs: 74 records = 19 groups over 8 warps; the peers' mailbox: 8 records): two
+    // sets of loads in flight; more (no clusters: 148 records): one set
+    const int nwarps = (int)(blockDim.x >> 5);
+    if (SYS) return poll_records_impl<SYS, 1, false>(recs, count, seq, stage, abort_word, deadline);
+    if (count <= 12 * nwarps) return poll_records_impl<SYS, 3, false>(recs, count, seq, stage, abort_word, deadline);
+    return poll_records_impl<SYS, POLL_GROUPS_MAX, false>(recs, count, seq, stage, abort_word, deadline);
 }
 // Warp-wide position of the (value, lowest index) winner: the REDUX rounds of best_warp_one on (f, idx), returning the
 // lane that holds it
@@ -687,7 +774,7 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
     const unsigned seq = (unsigned)gather_no + 1u;
     const unsigned parity = (unsigned)gather_no & 1u;
     const bool leader = crank == 0;
-    Rec *recs = a.rec + (size_t)(gather_no & 1) * SMO_MAX_RECS;
+    Rec *recs = a.rec + (size_t)(gather_no & 1) * SMO_REC_COPIES * SMO_MAX_RECS;      // [copy][record] of this generation
 
     // hop 1: this CTA's winners
     best_warp_reduce(mine);
@@ -717,13 +804,13 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
                 best_merge(b, sh.plo, sh.phi);
             }
             SVM_STAMP(5);
-            if (lane == 0) rec_store<false>(recs + cid, b, seq);           // hop 3: publish
+            rec_store_copies(recs, cid, b, seq, lane);                     // hop 3: publish
             SVM_STAMP(6);
         }
     }
     bool ok = true;
     if (leader) {
-        ok = poll_records<false>(recs, NC, seq, sh.recdata, a.abort_word, 0);
+        ok = poll_records<false>(recs + (size_t)(cid % SMO_REC_COPIES) * SMO_MAX_RECS, NC, seq, sh.recdata, a.abort_word, 0);
         SVM_STAMP(11);
         ok = __syncthreads_and(ok ? 1 : 0) != 0;          // every warp's share is staged
         SVM_STAMP(12);
@@ -731,11 +818,13 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
         SVM_STAMP(13);
         if (a.peers > 1) {
             // second level (row sharding): one record per GPU, stored into every peer's mailbox over NVLink (peer-mapped
-            // memory, same self-validating words at system scope) by the first leader, polled locally by every leader.
+            // memory, same self-validating words at system scope), polled locally by every leader.  The mailbox is kept in
+            // copies like the records: leader c < copies stores copy c everywhere, leader c polls copy c mod copies.
             // A peer that never shows up ends the wait after ~3 s; the abort word then ends every other wait on this GPU.
             const unsigned seq2 = ((unsigned)(a.epoch & 0x7ff) << 21) | seq;
-            const int slot = (gather_no & 1) * 8;
-            if (blockIdx.x == 0 && warp == 0 && lane < a.peers) rec_store<true>(a.peer_mailbox[lane] + slot + a.rank, mine, seq2);
+            const int gen = (gather_no & 1) * SMO_MB_COPIES;
+            if (cid < a.mailbox_copies && warp == 0) mailbox_store(a.peer_mailbox, a.peers, a.rank, (gen + cid) * 8, mine, seq2, lane);
+            const int slot = (gen + cid % a.mailbox_copies) * 8;
             __syncthreads();                               // the first level's staged words have been folded by every warp
             const bool ok2 = poll_records<true>(a.mailbox + slot, a.peers, seq2, sh.recdata, a.abort_word, clock64() + PEER_TIMEOUT_CLOCKS);
             ok = __syncthreads_and((ok && ok2) ? 1 : 0) != 0;
@@ -770,7 +859,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     constexpr int WARPS = THREADS / 32;
     using Vec = typename RowVec<XT>::type;
     const unsigned char *Xb = static_cast<const unsigned char *>(a.X);
-    const int row_bytes = a.pitch4 * 16;
+    // bytes of a row in the ring (uint8 rows: the main class only; the tails have their own array and buffer)
+    const int row_bytes = sizeof(XT) == 1 ? a.mw * 4 : a.pitch4 * 16;
     // shared-memory carve-up: [warps][slots] rows | mbarriers | Shared
     unsigned char *slots = smem_raw;
     const int KS = a.kslots;
@@ -791,10 +881,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     lists.pp = reinterpret_cast<double2 *>(sh_wt + a.tw * 4);
     lists.kk = reinterpret_cast<unsigned short *>(lists.pp + lists.cap * 4);
     lists.xlt = reinterpret_cast<unsigned char *>(lists.kk + lists.cap * 4);
-    // (uint8 rows, when it fits) per warp: the tail bytes of the 32 rows of a block, set aside group by group so that the
-    // block's rows are walked together, a lane per row; the odd pitch (in 16-byte units) spreads the rows over the banks
-    unsigned char *tailbuf = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(lists.xlt + a.tw * 4) + 15) & ~(uintptr_t)15) +
-                             (size_t)warp * 32 * a.tail_pitch;
+    // (uint8 rows) per warp: the tail bytes of a block of a.tail_rows rows, brought by one bulk copy from the tail array and
+    // walked a lane per row; the odd pitch (in 16-byte units) spreads the rows over the banks
+    unsigned char *tailbuf = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(lists.xlt + a.tw * 4) + 127) & ~(uintptr_t)127) +
+                             (size_t)warp * a.tail_rows * a.tail_pitch;
+    const unsigned char *Xt = Xb + (size_t)a.n * row_bytes;        // (uint8 rows) the tail array follows the main-class array
     if constexpr (IS_U8)
         for (int k = threadIdx.x; k < a.tw * 4; k += THREADS) sh_wt[k] = a.wt[k];
 
@@ -817,6 +908,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     uint64_t *my_bars = bars + warp * SMO_KSLOTS_MAX;
     if (lane == 0) {
         for (int s = 0; s < KS; ++s) mbar_init(&my_bars[s], 1);
+        if (IS_U8) mbar_init(&my_bars[SMO_KSLOTS_MAX - 1], 1);       // the tail blocks' barrier (the ring uses at most four of the eight)
         if (warp == 0) { mbar_init(&sh.bar_in, 1); mbar_init(&sh.bar_out, 1); }
         mbar_fence_init();
     }
@@ -845,8 +937,27 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         pf_row += nrows;
         if (pf_row >= m) pf_row = 0;
     };
-    if (m > 0)
+    if (m > 0 && row_bytes > 0)
         for (int s = 0; s < KS; ++s) issue_into(s);
+    // (uint8 rows) the tails: blocks of a.tail_rows consecutive rows of the warp's range, requested in order, cyclically, into
+    // the one buffer -- the next block is requested when the block at hand has been walked
+    uint64_t *tail_bar = &my_bars[SMO_KSLOTS_MAX - 1];
+    unsigned tphase = 0;
+    int tf_row = 0;                      // next row of the range whose tail to request
+    auto issue_tail = [&]() {
+        const int nrows = min(a.tail_rows, m - tf_row);
+        if (lane == 0) {
+            const int c = tf_row / a.tail_rows;
+            const bool keep = (((c + 1) * a.keep_per_1024) >> 10) != ((c * a.keep_per_1024) >> 10);
+            mbar_expect_tx(tail_bar, (unsigned)(nrows * a.tail_pitch));
+            bulk_g2s(tailbuf, Xt + (size_t)(w0 + tf_row) * a.tail_pitch, (unsigned)(nrows * a.tail_pitch), tail_bar,
+                     keep ? a.policy_keep : a.policy_stream);
+        }
+        tf_row += nrows;
+        if (tf_row >= m) tf_row = 0;
+    };
+    if constexpr (IS_U8)
+        if (m > 0 && a.tw > 0) issue_tail();
 
     // ---- exchange 0: selection over the initial state (main3.cpp:203-204 in the first iteration)
     LocalBest mine;
@@ -901,8 +1012,18 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         }
         const bool use_cache = hit_h && hit_l;
 
-        // cached iteration: this thread's first row of the pass is requested now, so that its loads and the K12 load
-        // below travel together instead of one L2 round trip after the other
+        // cached iteration: K12 is column i_low of the cached row of i_high -- the one read of a value another CTA wrote: it was
+        // stored by the CTA that owns row i_low, at least one exchange ago (its __threadfence in finish_row, this thread's fence
+        // here after the records it observed).  Read from L2: this SM's L1 may still hold the line from when the slot cached
+        // another row.  The fence comes first, while this thread has nothing in flight, then the K12 load and this thread's
+        // first rows of the pass are requested together instead of one L2 round trip after the other.
+        const bool local_low = i_low >= a.row_begin && i_low < a.row_end;
+        const bool k12_cached = use_cache && !gain && local_low;
+        double K12c = 1.0;
+        if (k12_cached) {
+            __threadfence();
+            K12c = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
+        }
         const long long pj = r0 + threadIdx.x, pj2 = pj + THREADS;
         double p_f = 0.0, p_a = 0.0, p_kh = 0.0, p_kl = 0.0, p2_f = 0.0, p2_a = 0.0, p2_kh = 0.0, p2_kl = 0.0;
         int p_y = 0, p2_y = 0;
@@ -928,10 +1049,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         if constexpr (IS_U8) {
           // pivots are needed for an X pass, and for K12 of a cached iteration whose row i_low lives on another GPU (row sharding:
           // X is replicated, so K12 is formed here the way that GPU formed it)
-          const bool local_low = i_low >= a.row_begin && i_low < a.row_end;
           if (!use_cache || (!gain && !local_low)) {
             const unsigned *xh = reinterpret_cast<const unsigned *>(Xb + (size_t)i_high * row_bytes);
             const unsigned *xl = reinterpret_cast<const unsigned *>(Xb + (size_t)piv_l * row_bytes);
+            const unsigned *th = reinterpret_cast<const unsigned *>(Xt + (size_t)i_high * a.tail_pitch);
+            const unsigned *tl = reinterpret_cast<const unsigned *>(Xt + (size_t)piv_l * a.tail_pitch);
 #pragma unroll
             for (int i = 0; i < MSLOTS; ++i) {                  // a.mw == 32 * MSLOTS
                 pm_h[i] = __ldg(xh + i * 32 + lane);
@@ -939,7 +1061,7 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             }
             nm_h = a.nmain[i_high]; nm_l = a.nmain[piv_l];
             n_h = a.ntail[i_high]; n_l = a.ntail[piv_l];
-            lcnt = u8_build_lists(xh + a.mw, xl + a.mw, sh_wt, lists, lane);
+            lcnt = u8_build_lists(th, tl, sh_wt, lists, lane);
             SVM_STAMP(15);
             int dot = 0;
 #pragma unroll
@@ -951,11 +1073,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
             double tail = (n_l + n_h) - 2.0 * dh;
             if (tail < 0.0) tail = 0.0;
             K12 = svm_exp(-a.gamma * fma((double)S, a.wR, tail));
-          } else if (gain) {
-            K12 = 1.0;                                          // not used: a gain pass makes no step
           } else {
-            __threadfence();
-            K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
+            K12 = K12c;                                         // a gain pass makes no step: its K12 (1.0) is not used
           }
         } else
         if (!use_cache) {
@@ -975,14 +1094,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 if (i * 32 + lane < a.pitch4) accum_pair<CH>(pv.l[i], pv.h[i], acc);
             acc = warp_sum_butterfly(acc);
             K12 = svm_exp(-a.gamma * dist2<XT>(n_h, n_l, acc));
-        } else if (gain) {
-            K12 = 1.0;                                              // not used: a gain pass makes no step
-        } else if (i_low >= a.row_begin && i_low < a.row_end) {
-            // the one read of a value another CTA wrote: column i_low of the cached row was stored by the CTA that
-            // owns row i_low, at least one exchange ago (its __threadfence below, this thread's fence here after the
-            // records it observed).  Read it from L2: this SM's L1 may still hold the line from when the slot cached another row.
-            __threadfence();
-            K12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
+        } else if (gain || local_low) {
+            K12 = K12c;                                             // a gain pass makes no step: its K12 (1.0) is not used
         } else {
             // row sharding: column i_low of the cached rows lives on the GPU that owns row i_low; X is
             // replicated, so form K12 here the way that GPU formed it (same code, same bits)
@@ -1038,8 +1151,8 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
               // ---------------- uint8 rows: a warp per group of eight rows ----------------
               // both sections of a row are padded with zero bytes to whole 128-byte slots (32 lanes x one word), so a lane's
               // words sit at constant offsets from one address per row and need no bounds test
-              const int tail_off = a.mw * 4;
-              const bool tail_block = a.tail_pitch > 0;
+              const bool has_tail = a.tw > 0;
+              const int TB = a.tail_rows;
               const int n0 = __shfl_sync(FULL, lcnt, 0), n1 = __shfl_sync(FULL, lcnt, 1), n2 = __shfl_sync(FULL, lcnt, 2), n3 = __shfl_sync(FULL, lcnt, 3);
               SVM_PH_DECL;
               for (int base = 0; base < m; base += 32) {
@@ -1050,85 +1163,76 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 long long qj = -1;
                 if (lane < cnt) { fj = a.f[j]; aj = a.alpha[j]; yj = a.y[j]; nmj = a.nmain[j]; ntj = a.ntail[j]; if (a.cacheq) qj = a.cacheq[j]; }
                 int my_sh = 0, my_sl = 0;                  // the integer dot products of this lane's row of the block
+                double2 dd = make_double2(0.0, 0.0);       // D(row, pivots) over the tail of this lane's row
                 for (int t = 0; t < cnt; t += RPS) {
                     const int rows_here = min(RPS, cnt - t);
-                    SVM_PH(5);
-                    mbar_wait(&my_bars[cslot], cphase);
-                    SVM_PH(0);
-                    const unsigned char *grp = my_slots + (size_t)cslot * RPS * row_bytes;
-                    int SI[2 * RPS];                       // [pivot * RPS + row] integer dot products over the main class
+                    if constexpr (MSLOTS > 0) {
+                        SVM_PH(5);
+                        mbar_wait(&my_bars[cslot], cphase);
+                        SVM_PH(0);
+                        const unsigned char *grp = my_slots + (size_t)cslot * RPS * row_bytes;
+                        int SI[2 * RPS];                   // [pivot * RPS + row] integer dot products over the main class
 #pragma unroll
-                    for (int k = 0; k < 2 * RPS; ++k) SI[k] = 0;
-                    // main class: eight rows side by side (sixteen independent sums), or four when the group is the short one that
-                    // ends the warp's range: rows beyond the group's last hold bytes of an earlier group, their sums are never read
-                    const unsigned char *lanep = grp + lane * 4;
-                    if (rows_here > 4) u8_main_sums<QM, MSLOTS, RPS, 8>(lanep, row_bytes, pm_h, pm_l, SI);
-                    else u8_main_sums<QM, MSLOTS, RPS, 4>(lanep, row_bytes, pm_h, pm_l, SI);
-                    SVM_PH(1);
-                    if (tail_block) {
-                        // tail: set the group's tail bytes aside (16-byte chunks; the block's rows are walked together below)
-                        // eight lanes per row (128 contiguous bytes: all banks once), rows r and r + 4 (tw is a multiple of 32 words:
-                        // a multiple of 8 chunks per row)
-                        const int chunks = a.tw >> 2;
-                        const int r = lane >> 3, q0 = (lane & 7) * 16;
-                        const unsigned char *src = grp + (size_t)r * row_bytes + tail_off + q0;
-                        unsigned char *dst = tailbuf + (size_t)(t + r) * a.tail_pitch + q0;
-                        for (int q = 0; q < chunks; q += 8) {
-                            uint4 v0 = make_uint4(0u, 0u, 0u, 0u), v1 = v0;
-                            if (r < rows_here) v0 = *reinterpret_cast<const uint4 *>(src + q * 16);
-                            if (r + 4 < rows_here) v1 = *reinterpret_cast<const uint4 *>(src + 4 * (size_t)row_bytes + q * 16);
-                            if (r < rows_here) *reinterpret_cast<uint4 *>(dst + q * 16) = v0;
-                            if (r + 4 < rows_here) *reinterpret_cast<uint4 *>(dst + 4 * (size_t)a.tail_pitch + q * 16) = v1;
+                        for (int k = 0; k < 2 * RPS; ++k) SI[k] = 0;
+                        // main class: eight rows side by side (sixteen independent sums), or four when the group is the short one that
+                        // ends the warp's range: rows beyond the group's last hold bytes of an earlier group, their sums are never read
+                        const unsigned char *lanep = grp + lane * 4;
+                        if (rows_here > 4) u8_main_sums<QM, MSLOTS, RPS, 8>(lanep, row_bytes, pm_h, pm_l, SI);
+                        else u8_main_sums<QM, MSLOTS, RPS, 4>(lanep, row_bytes, pm_h, pm_l, SI);
+                        SVM_PH(1);
+                        __syncwarp();
+                        fence_proxy_async();
+                        issue_into(cslot);
+                        if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
+                        SVM_PH(3);
+                        // the integer sums are exact in any order: the hardware warp reduction, the row's own lane keeps the result
+#pragma unroll
+                        for (int r = 0; r < RPS; ++r) {
+                            const int sh_ = __reduce_add_sync(FULL, SI[r]), sl_ = __reduce_add_sync(FULL, SI[RPS + r]);
+                            if (lane == t + r) { my_sh = sh_; my_sl = sl_; }
                         }
-                    } else {
-                        // tail (too long for the buffer): four lanes per row walk the sub-lists of the pivots' non-zero positions
-                        const int r = lane >> 2;
-                        double dh, dl;
-                        u8_tail_dots(grp + (size_t)r * row_bytes + tail_off, r < rows_here ? lcnt : 0, lists, lane, dh, dl);
-                        if (!(lane & 3) && r < rows_here) stage[t + r] = make_double2(dh, dl);
+                        SVM_PH(4);
                     }
-                    SVM_PH(2);
-                    __syncwarp();
-                    fence_proxy_async();
-                    issue_into(cslot);
-                    if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
-                    SVM_PH(3);
-                    // the integer sums are exact in any order: the hardware warp reduction, the row's own lane keeps the result
+                    // tail: when the rows of a tail block are through, a lane per row walks the four sub-lists one after the other
+                    // (uniform trip counts, broadcast reads of the entries), then the buffer is handed back for the next block
+                    const int done = t + rows_here;
+                    if (has_tail && ((done & (TB - 1)) == 0 || done == cnt)) {
+                        const int c0 = (done - 1) & ~(TB - 1);         // first row of the tail block within the 32-row block
+                        mbar_wait(tail_bar, tphase);
+                        tphase ^= 1u;
+                        SVM_PH(2);
+                        if (lane < done - c0) {
+                            const unsigned char *myrow = tailbuf + (size_t)lane * a.tail_pitch;
+                            double sh_[4] = {0.0, 0.0, 0.0, 0.0}, sl_[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-                    for (int r = 0; r < RPS; ++r) {
-                        const int sh_ = __reduce_add_sync(FULL, SI[r]), sl_ = __reduce_add_sync(FULL, SI[RPS + r]);
-                        if (lane == t + r) { my_sh = sh_; my_sl = sl_; }
+                            for (int c = 0; c < 4; ++c)                 // the first four entries of every sub-list, no branch between them
+                                u8_walk4(myrow, lists.pp + c * lists.cap, lists.kk + c * lists.cap, 0, sh_[c], sl_[c]);
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                const int n = c == 0 ? n0 : c == 1 ? n1 : c == 2 ? n2 : n3;
+                                for (int e = 4; e < n; e += 4) u8_walk4(myrow, lists.pp + c * lists.cap, lists.kk + c * lists.cap, e, sh_[c], sl_[c]);
+                            }
+                            dd = make_double2((sh_[0] + sh_[1]) + (sh_[2] + sh_[3]), (sl_[0] + sl_[1]) + (sl_[2] + sl_[3]));
+                            if (TB < 32) stage[c0 + lane] = dd;        // parked until the row's own lane finishes the row
+                        }
+                        __syncwarp();
+                        fence_proxy_async();
+                        issue_tail();
+                        SVM_PH(6);
                     }
-                    SVM_PH(4);
                 }
                 __syncwarp();
-                SVM_PH(5);
-                double2 dd;
-                if (tail_block) {
-                    // a lane per row: the four sub-lists one after the other (uniform trip counts, broadcast reads of the entries)
-                    const unsigned char *myrow = tailbuf + (size_t)lane * a.tail_pitch;
-                    double sh_[4] = {0.0, 0.0, 0.0, 0.0}, sl_[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c)                     // the first four entries of every sub-list, no branch between them
-                        u8_walk4(myrow, lists.pp + c * lists.cap, lists.kk + c * lists.cap, 0, sh_[c], sl_[c]);
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const int n = c == 0 ? n0 : c == 1 ? n1 : c == 2 ? n2 : n3;
-                        for (int e = 4; e < n; e += 4) u8_walk4(myrow, lists.pp + c * lists.cap, lists.kk + c * lists.cap, e, sh_[c], sl_[c]);
-                    }
-                    dd = make_double2((sh_[0] + sh_[1]) + (sh_[2] + sh_[3]), (sl_[0] + sl_[1]) + (sl_[2] + sl_[3]));
-                } else if (lane < cnt) dd = stage[lane];
+                if (has_tail && TB < 32 && lane < cnt) dd = stage[lane];
                 if (lane < cnt) {
-                    const int2 ii = make_int2(my_sh, my_sl);
                     double t_h = (ntj + n_h) - 2.0 * dd.x, t_l = (ntj + n_l) - 2.0 * dd.y;
                     if (t_h < 0.0) t_h = 0.0;
                     if (t_l < 0.0) t_l = 0.0;
-                    const double kh = svm_exp(-a.gamma * fma((double)(nmj + nm_h - 2 * ii.x), a.wR, t_h));
-                    const double kl = svm_exp(-a.gamma * fma((double)(nmj + nm_l - 2 * ii.y), a.wR, t_l));
+                    const double kh = svm_exp(-a.gamma * fma((double)(nmj + nm_h - 2 * my_sh), a.wR, t_h));
+                    const double kl = svm_exp(-a.gamma * fma((double)(nmj + nm_l - 2 * my_sl), a.wR, t_l));
                     finish_row(a, it, j, fj, aj, yj, qj, kh, kl, acc_best);
                 }
                 __syncwarp();                                  // the parked sums have been read: the next block may overwrite them
-                SVM_PH(6);
+                SVM_PH(7);
               }
               SVM_PH_FLUSH;
             } else if constexpr (RPS > 1) {
@@ -1296,11 +1400,13 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
     }
 
     // drain the ring: every requested copy must land before the CTA may exit
-    if (m > 0)
+    if (m > 0 && row_bytes > 0)
         for (int k = 0; k < KS; ++k) {
             mbar_wait(&my_bars[cslot], cphase);
             if (++cslot == KS) { cslot = 0; cphase ^= 1u; }
         }
+    if constexpr (IS_U8)
+        if (m > 0 && a.tw > 0) mbar_wait(tail_bar, tphase);      // and the tail block requested last
     cluster_sync_all();                  // no CTA leaves while its partner may still write into its shared memory
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         SmoResult r;
@@ -1329,14 +1435,14 @@ __global__ void peer_rendezvous_kernel(PeerFlags pf, int rank, int peers, unsign
     }
 }
 
-// kslots: ring depth per warp in slots; a slot holds rows_per_step rows
-inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1, int tail_words = 0, int tail_pitch = 0)
+// kslots: ring depth per warp in slots; a slot holds rows_per_step rows of pitch4 16-byte groups (uint8 rows: of the main class)
+inline size_t smo_smem_bytes(int pitch4, int kslots, int warps, int rows_per_step = 1, int tail_words = 0, int tail_pitch = 0, int tail_rows = 32)
 {
     return (size_t)warps * kslots * rows_per_step * pitch4 * 16 + sizeof(uint64_t) * warps * SMO_KSLOTS_MAX + sizeof(Shared) + 128 +
            (size_t)warps * 32 * (sizeof(double2) + sizeof(int2)) +   // + the parked sums of the rows-in-groups passes
            (size_t)tail_words * 4 * (sizeof(double) + 1) + (size_t)(tail_words + 4) * 4 * (sizeof(double2) + sizeof(unsigned short)) + 32 +  // + the tail weights and the
                                                                      //   sub-lists of the pivots' non-zero tail positions (uint8 rows)
-           (size_t)warps * 32 * tail_pitch;                          // + the blocks' tails set aside
+           (tail_pitch ? 128 + (size_t)warps * tail_rows * tail_pitch : 0);   // + the buffers of the tail blocks
 }
 
 } // namespace svm

@@ -1,5 +1,5 @@
 """Where the uint8 pass of CTA 0's warp 0 spends its cycles (profiling build libsvmb200_timing.so): per iteration the sums of
-wait-for-data, main-class sums, tail, refill (fence + bulk copy issue), integer reduce, row loads / loop, finishing."""
+wait-for-data, main-class sums, refill (fence + bulk copy issue), integer reduce, row loads / loop, tail walk, finishing."""
 import ctypes as C, os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -17,10 +17,11 @@ rows = min(4000, o["num_iter"] - 2)
 t = np.zeros((rows, 8), dtype=np.int64)
 assert s.L.svmb200_debug_timing_pass(t.ctypes.data_as(C.c_void_p), rows) == 0
 t = t[20:]
-names = ["wait for the group's bytes", "main-class sums (LDS + IDP4A)", "tail walk + combine", "fence + refill issue", "integer warp reduce", "block setup (row state loads, loop)", "finishing (exp, f update, selection)", "-"]
+names = ["wait for the group's bytes", "main-class sums (LDS + IDP4A)", "wait for the tail block's bytes", "fence + refill issue", "integer warp reduce",
+         "block setup (row state loads, loop)", "tail walk (a lane per row) + refill issue", "finishing (exp, f update, selection)"]
 print(f"n={n} us/iter={1e3 * o['smo_ms'] / (o['num_iter'] - 1):.2f}; cycles of warp 0 of CTA 0 per iteration (median), 1.965 GHz")
 tot = 0
-for i, nm in enumerate(names[:7]):
+for i, nm in enumerate(names):
     v = np.median(t[:, i]); tot += v
     print(f"  {nm:40s} {v:9.0f} cyc = {v / 1965:6.2f} us")
 print(f"  {'sum':40s} {tot:9.0f} cyc = {tot / 1965:6.2f} us")
