@@ -223,6 +223,9 @@ typedef struct {
     double  train_ms;        /* wall time of the call */
     int64_t smo_iterations;  /* SMO iterations of this rank's stages */
     int32_t stages;          /* SMO_train calls of this rank */
+    double  solve_ms;        /* wall time of this rank's stages: labels up, packing, SMO, extraction of the support vectors */
+    double  smo_ms;          /* of which inside the SMO kernels (CUDA events); train_ms - solve_ms = exchange of tuples, merging,
+                              * and waiting for other ranks' stages */
 } svmb200_cascade_stats;
 int svmb200_cascade_unique_id(void *id128);
 int svmb200_cascade_connect(svmb200_ctx *ctx, int32_t rank, int32_t world, const void *id128);

@@ -38,7 +38,7 @@ class Stats(C.Structure):
 
 class CascadeStats(C.Structure):
     _fields_ = [("rounds", C.c_int32), ("converged", C.c_int32), ("n_sv", C.c_int32), ("b", C.c_double), ("train_ms", C.c_double),
-                ("smo_iterations", C.c_int64), ("stages", C.c_int32)]
+                ("smo_iterations", C.c_int64), ("stages", C.c_int32), ("solve_ms", C.c_double), ("smo_ms", C.c_double)]
 
 
 def declared_symbols() -> list[str]:

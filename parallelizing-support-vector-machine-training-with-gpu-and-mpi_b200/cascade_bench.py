@@ -93,9 +93,11 @@ def run(pkg, solver, X, y, rank, world, local_rank, args, digits=None):
     modes = ["star"] + (["tree"] if world & (world - 1) == 0 else [])
     for mode in modes:
         run_gpu(s, X[: max(2000, world * 64)], y[: max(2000, world * 64)], rank, world, mode)           # warm-up (module load, NCCL channels)
-        out = run_gpu(s, X, y, rank, world, mode)
-        rec = {"secs": out["secs"], "rounds": out["rounds"], "converged": bool(out["converged"]), "n_sv": out["n_sv"], "b": out["b"],
-               "stages_on_rank0": out["stages"], "smo_iterations_on_rank0": out["smo_iterations"]}
+        outs = [run_gpu(s, X, y, rank, world, mode) for _ in range(2)]         # the whole job twice; the faster run is reported, both are listed
+        out = min(outs, key=lambda o: o["secs"])
+        rec = {"secs": out["secs"], "secs_of_each_run": [o["secs"] for o in outs], "rounds": out["rounds"], "converged": bool(out["converged"]),
+               "n_sv": out["n_sv"], "b": out["b"], "stages_on_rank0": out["stages"], "smo_iterations_on_rank0": out["smo_iterations"],
+               "stage_secs_on_rank0": out["solve_ms"] / 1e3, "smo_kernel_secs_on_rank0": out["smo_ms"] / 1e3}
         if rank == 0 and g is not None:
             ids, _ = s.cascade_get_model()
             rec["sv_set_equals_undivided_reference"] = bool(np.array_equal(np.sort(ids), g["sv_ids"]))

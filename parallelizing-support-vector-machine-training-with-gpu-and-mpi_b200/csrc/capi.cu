@@ -887,10 +887,14 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     }
     if (cache_cap == 1) cache_cap = 2;
     if (cache_cap > 0 && (size_t)cache_cap * n > ctx->cacheK_elems) {     // sized in elements: the same capacity needs more room when n grows
+        // a context that is trained again and again on sets of changing size (the cascade's stages) should not free and
+        // allocate gigabytes per call: grow by at least a half, up to the automatic budget
+        size_t want = (size_t)cache_cap * n;
+        if (ctx->cacheK_elems) want = std::max(want, std::min(ctx->cacheK_elems + ctx->cacheK_elems / 2, ((size_t)8 << 30) / sizeof(double)));
         if (dev_free(ctx, ctx->cacheK)) return SVMB200_ECUDA;
         ctx->cacheK_elems = 0;
-        CK(cudaMalloc(&ctx->cacheK, (size_t)cache_cap * n * sizeof(double)));
-        ctx->cacheK_elems = (size_t)cache_cap * n;
+        CK(cudaMalloc(&ctx->cacheK, want * sizeof(double)));
+        ctx->cacheK_elems = want;
     }
 
     const size_t rec_bytes = (size_t)2 * SMO_REC_COPIES * SMO_MAX_RECS * sizeof(Rec) + 256;     // two generations of records (in copies) + the abort word

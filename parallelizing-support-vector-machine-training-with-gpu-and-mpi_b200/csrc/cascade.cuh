@@ -102,6 +102,7 @@ struct CascadeState {
     double model_b = 0.0;
     long long smo_iterations = 0;
     int stages = 0;
+    double solve_ms = 0.0, smo_ms = 0.0;      // wall time of this rank's stages (upload of labels, packing, SMO, SV extraction); SMO kernels alone
 };
 
 // out[k] = src[sel[k]] (rows of d bytes, d a multiple of 4 or not: byte-wise in words where aligned)
@@ -218,6 +219,11 @@ static int cas_solve_stage(svmb200_ctx *ctx, svm::CascadeState *cas, const std::
     out.meta.clear();
     *b_out = 0.0;
     if (n == 0) return 0;
+    struct StageClock {
+        double *acc;
+        std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+        ~StageClock() { *acc += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+    } stage_clock{&cas->solve_ms};
     ctx->storage_resolved = SVMB200_STORAGE_U8;
     if (int rc = alloc_train(ctx, n, d)) return rc;
     CK(cudaMemcpyAsync(ctx->minv, cas->gmin, (size_t)d * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
@@ -238,6 +244,7 @@ static int cas_solve_stage(svmb200_ctx *ctx, svm::CascadeState *cas, const std::
     if (int rc = svmb200_smo_train(ctx, &p, alpha.data(), &b, &st)) return rc;
     cas->smo_iterations += st.num_iter - 1;
     cas->stages += 1;
+    cas->smo_ms += st.smo_ms;
     *b_out = b;
     std::vector<int> idx;
     for (long long i = 0; i < n; ++i)
@@ -535,6 +542,20 @@ int svmb200_cascade_connect(svmb200_ctx *ctx, int32_t rank, int32_t world, const
     ctx->cascade = cas;
     NCK(N.CommInitRank(&cas->comm, world, id, rank));
     CK(cudaMalloc(&cas->count_dev, (size_t)(2 * world + 2) * sizeof(int)));
+    CK(cudaMemsetAsync(cas->count_dev, 0, (size_t)(2 * world + 2) * sizeof(int), ctx->stream));
+    // NCCL builds a collective's rings and a pair's point-to-point channels on first use (hundreds of milliseconds): one tiny
+    // call of each kind the round loops make, and one message along every edge of the tree, happen here, like MPI_Init, not
+    // inside the first round
+    NCK(N.AllGather(cas->count_dev + world, cas->count_dev, 1, svm::ncclInt32, cas->comm, ctx->stream));
+    NCK(N.Broadcast(cas->count_dev, cas->count_dev, 1, svm::ncclInt32, 0, cas->comm, ctx->stream));
+    NCK(N.AllReduce(cas->count_dev + world, cas->count_dev + world, 1, svm::ncclInt32, svm::ncclMax, cas->comm, ctx->stream));
+    NCK(N.GroupStart());
+    for (int step = 1; step < world; step *= 2) {          // mpi_svm_main3.cpp:689-716: rank r receives from r + step, r + step sends to r
+        if (rank % (2 * step) == 0 && rank + step < world) NCK(N.Recv(cas->count_dev + world + 1, 1, svm::ncclInt32, rank + step, cas->comm, ctx->stream));
+        else if (rank % (2 * step) == step) NCK(N.Send(cas->count_dev + world, 1, svm::ncclInt32, rank - step, cas->comm, ctx->stream));
+    }
+    NCK(N.GroupEnd());
+    CK(cudaStreamSynchronize(ctx->stream));
     return SVMB200_OK;
 }
 
@@ -587,6 +608,7 @@ int svmb200_cascade_train(svmb200_ctx *ctx, int32_t mode, const svmb200_params *
     CK(cudaSetDevice(ctx->device));
     cas->smo_iterations = 0;
     cas->stages = 0;
+    cas->solve_ms = cas->smo_ms = 0.0;
     int rounds = 0, converged = 0;
     const auto t0 = std::chrono::steady_clock::now();
     const int rc = mode == SVMB200_CASCADE_STAR ? cas_run_star(ctx, cas, params, max_rounds, &rounds, &converged)
@@ -621,6 +643,8 @@ int svmb200_cascade_train(svmb200_ctx *ctx, int32_t mode, const svmb200_params *
         stats->train_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         stats->smo_iterations = cas->smo_iterations;
         stats->stages = cas->stages;
+        stats->solve_ms = cas->solve_ms;
+        stats->smo_ms = cas->smo_ms;
     }
     return SVMB200_OK;
 }

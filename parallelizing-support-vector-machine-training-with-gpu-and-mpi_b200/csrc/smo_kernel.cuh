@@ -377,18 +377,30 @@ __device__ __forceinline__ unsigned long long order_key(double f)
     const unsigned long long u = (unsigned long long)__double_as_longlong(f + 0.0);
     return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
 }
-template <bool IS_MIN>
-__device__ __forceinline__ void best_warp_one(Best &b)
+// The lanes that hold the (value, lowest index) minimum of (flo, ilo) and maximum of (fhi, ihi).  The rounds of the two
+// sides are issued side by side (a REDUX takes tens of cycles: the sides hide each other's latency); the round on the
+// index runs only when more than one lane holds the winning value.
+__device__ __forceinline__ void warp_arg_best2(double flo, int ilo, double fhi, int ihi, int &src_lo, int &src_hi)
 {
-    unsigned long long key = order_key(b.f);
-    if (!IS_MIN) key = ~key;
-    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-    const unsigned mhi = __reduce_min_sync(FULL, hi);
-    const unsigned mlo = __reduce_min_sync(FULL, hi == mhi ? lo : 0xffffffffu);
-    const bool tie = hi == mhi && lo == mlo;
-    const unsigned midx = __reduce_min_sync(FULL, tie ? (unsigned)b.idx : 0xffffffffu);
-    const unsigned holders = __ballot_sync(FULL, tie && (unsigned)b.idx == midx);   // a row index lives in exactly one lane
-    const int src = __ffs(holders) - 1;
+    const unsigned long long ka = order_key(flo), kb = ~order_key(fhi);
+    const unsigned ah = (unsigned)(ka >> 32), al = (unsigned)ka, bh = (unsigned)(kb >> 32), bl = (unsigned)kb;
+    const unsigned mah = __reduce_min_sync(FULL, ah), mbh = __reduce_min_sync(FULL, bh);
+    const unsigned mal = __reduce_min_sync(FULL, ah == mah ? al : 0xffffffffu), mbl = __reduce_min_sync(FULL, bh == mbh ? bl : 0xffffffffu);
+    const bool ta = ah == mah && al == mal, tb = bh == mbh && bl == mbl;
+    unsigned ba = __ballot_sync(FULL, ta), bb = __ballot_sync(FULL, tb);
+    if (ba & (ba - 1)) {                                   // warp-uniform: several lanes hold the minimum
+        const unsigned midx = __reduce_min_sync(FULL, ta ? (unsigned)ilo : 0xffffffffu);
+        ba = __ballot_sync(FULL, ta && (unsigned)ilo == midx);
+    }
+    if (bb & (bb - 1)) {
+        const unsigned midx = __reduce_min_sync(FULL, tb ? (unsigned)ihi : 0xffffffffu);
+        bb = __ballot_sync(FULL, tb && (unsigned)ihi == midx);
+    }
+    src_lo = __ffs(ba) - 1;                                // lanes that tie on the index too hold the same row (or no row): any of them
+    src_hi = __ffs(bb) - 1;
+}
+__device__ __forceinline__ void best_take(Best &b, int src)
+{
     b.f = __shfl_sync(FULL, b.f, src);
     b.alpha = __shfl_sync(FULL, b.alpha, src);
     b.q = __shfl_sync(FULL, b.q, src);
@@ -397,8 +409,10 @@ __device__ __forceinline__ void best_warp_one(Best &b)
 }
 __device__ __forceinline__ void best_warp_reduce(LocalBest &b)
 {
-    best_warp_one<true>(b.lo);
-    best_warp_one<false>(b.hi);
+    int src_lo, src_hi;
+    warp_arg_best2(b.lo.f, b.lo.idx, b.hi.f, b.hi.idx, src_lo, src_hi);
+    best_take(b.lo, src_lo);
+    best_take(b.hi, src_hi);
 }
 __device__ __forceinline__ void best_merge(LocalBest &b, const Best &lo, const Best &hi)
 {
@@ -499,17 +513,6 @@ __device__ __forceinline__ void rec_unpack32(const unsigned *d, LocalBest &b)
     b.hi.y = (int)d[11];
     b.lo.q = (long long)(((unsigned long long)d[13] << 32) | d[12]);
     b.hi.q = (long long)(((unsigned long long)d[15] << 32) | d[14]);
-}
-template <bool SYS>
-__device__ __forceinline__ void rec_store(Rec *r, const LocalBest &b, unsigned seq)
-{
-#pragma unroll
-    for (int k = 0; k < REC_WORDS; k += 2) {
-        const unsigned long long v0 = ((unsigned long long)seq << 32) | rec_word(b, k);
-        const unsigned long long v1 = ((unsigned long long)seq << 32) | rec_word(b, k + 1);
-        if (SYS) asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
-        else asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&r->w[k]), "l"(v0), "l"(v1) : "memory");
-    }
 }
 // the word pair `pair` (0..7) of a record
 __device__ __forceinline__ void rec_word_pair(const LocalBest &b, int pair, unsigned &d0, unsigned &d1)
@@ -719,20 +722,6 @@ __device__ __forceinline__ bool poll_records(const Rec *recs, int count, unsigne
     if (count <= 12 * nwarps) return poll_records_impl<SYS, 3, false>(recs, count, seq, stage, abort_word, deadline);
     return poll_records_impl<SYS, POLL_GROUPS_MAX, false>(recs, count, seq, stage, abort_word, deadline);
 }
-// Warp-wide position of the (value, lowest index) winner: the REDUX rounds of best_warp_one on (f, idx), returning the
-// lane that holds it
-template <bool IS_MIN>
-__device__ __forceinline__ int warp_arg_best(double f, int idx)
-{
-    unsigned long long key = order_key(f);
-    if (!IS_MIN) key = ~key;
-    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-    const unsigned mhi = __reduce_min_sync(FULL, hi);
-    const unsigned mlo = __reduce_min_sync(FULL, hi == mhi ? lo : 0xffffffffu);
-    const bool tie = hi == mhi && lo == mlo;
-    const unsigned midx = __reduce_min_sync(FULL, tie ? (unsigned)idx : 0xffffffffu);
-    return __ffs(__ballot_sync(FULL, tie && (unsigned)idx == midx)) - 1;
-}
 // every warp folds the staged records by itself: lane l compares (f, idx) of records l, l + 32, ..., one REDUX round
 // per side finds the winning record, and every lane reads that record's payload
 __device__ __forceinline__ void fold_staged(unsigned (*stage)[REC_STRIDE], int count, LocalBest &g)
@@ -747,8 +736,10 @@ __device__ __forceinline__ void fold_staged(unsigned (*stage)[REC_STRIDE], int c
         if (better_min(f0, i0, flo, ilo)) { flo = f0; ilo = i0; rlo = r; }
         if (better_max(f1, i1, fhi, ihi)) { fhi = f1; ihi = i1; rhi = r; }
     }
-    rlo = __shfl_sync(FULL, rlo, warp_arg_best<true>(flo, ilo));
-    rhi = __shfl_sync(FULL, rhi, warp_arg_best<false>(fhi, ihi));
+    int src_lo, src_hi;
+    warp_arg_best2(flo, ilo, fhi, ihi, src_lo, src_hi);
+    rlo = __shfl_sync(FULL, rlo, src_lo);
+    rhi = __shfl_sync(FULL, rhi, src_hi);
     const unsigned *a = stage[rlo], *b = stage[rhi];
     g.lo.f = __hiloint2double((int)a[1], (int)a[0]);
     g.lo.idx = (int)a[2];
