@@ -625,6 +625,7 @@ struct __align__(16) Shared {
     Best plo, phi;                                // cluster leader: the partner CTA's winners (written through DSMEM)
     Best rlo, rhi;                                // partner CTA: the grid's winners (written through DSMEM by the leader)
     uint64_t bar_in, bar_out;                     // mbarriers of the two cluster hops
+    double k12;                                   // K12 of a cached iteration, read from L2 by one thread of the CTA
     unsigned recdata[SMO_MAX_RECS][REC_STRIDE];   // data words of the polled records (odd stride: lane l reads record l without bank conflicts)
 };
 
@@ -1006,14 +1007,16 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
         // cached iteration: K12 is column i_low of the cached row of i_high -- the one read of a value another CTA wrote: it was
         // stored by the CTA that owns row i_low, at least one exchange ago (its __threadfence in finish_row, this thread's fence
         // here after the records it observed).  Read from L2: this SM's L1 may still hold the line from when the slot cached
-        // another row.  The fence comes first, while this thread has nothing in flight, then the K12 load and this thread's
-        // first rows of the pass are requested together instead of one L2 round trip after the other.
+        // another row.  ONE thread of the CTA reads it (loads of one line from many SMs and warps serialise in L2: with every
+        // warp reading, this step cost 2 us of a 6 us iteration) and hands it to the others through shared memory, behind the
+        // CTA barrier below; its fence comes first, while it has nothing in flight, and the K12 load and every thread's first
+        // rows of the pass are requested together instead of one L2 round trip after the other.
         const bool local_low = i_low >= a.row_begin && i_low < a.row_end;
-        const bool k12_cached = use_cache && !gain && local_low;
+        const bool k12_cached = use_cache && !gain && local_low;            // uniform over the CTA (replicated state)
         double K12c = 1.0;
-        if (k12_cached) {
+        if (k12_cached && threadIdx.x == 0) {
             __threadfence();
-            K12c = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
+            sh.k12 = __ldcg(&a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + i_low]);
         }
         const long long pj = r0 + threadIdx.x, pj2 = pj + THREADS;
         double p_f = 0.0, p_a = 0.0, p_kh = 0.0, p_kl = 0.0, p2_f = 0.0, p2_a = 0.0, p2_kh = 0.0, p2_kl = 0.0;
@@ -1028,6 +1031,11 @@ __global__ void __launch_bounds__(THREADS, 1) smo_persistent_kernel(const __grid
                 p2_kh = a.cacheK[(size_t)(q_h % a.cache_cap) * a.n + pj2];
                 p2_kl = a.cacheK[(size_t)(q_l % a.cache_cap) * a.n + pj2];
             }
+        }
+
+        if (k12_cached) {
+            __syncthreads();                       // the next write of sh.k12 is at least one exchange (a CTA barrier) away
+            K12c = sh.k12;
         }
 
         // K12 = K(i_high, i_low)  (main3.cpp:241)

@@ -13,5 +13,5 @@ print('f32', d['paths']['f32_rows']['us_per_iter'], 'f64', d['paths']['f64_rows'
 print('parity u8', d['parity'].get('u8_rows',{}).get('meets_north_star'), d['parity'].get('u8_rows',{}).get('iterations'))
 PY
 timeout -k 10 300 python profiles/timeline_r2.py 60000 600 0 u8 > gpurun_out/timeline_u8.txt 2>&1; echo "timeline rc=$?" >> $S; head -19 gpurun_out/timeline_u8.txt >> $S
-timeout -k 10 300 python profiles/timeline_r2.py 60000 3000 -1 u8 > gpurun_out/timeline_u8_cache.txt 2>&1; echo "timeline cache rc=$?" >> $S; grep -A14 "cached" gpurun_out/timeline_u8_cache.txt | head -16 >> $S
+timeout -k 10 300 python profiles/timeline_r2.py 60000 3000 -1 u8 > gpurun_out/timeline_u8_cache.txt 2>&1; echo "timeline cache rc=$?" >> $S; grep -A15 "cached" gpurun_out/timeline_u8_cache.txt | head -17 >> $S
 cat $S

@@ -29,7 +29,7 @@ ghz = 1.965
 print(f"n={n} storage={storage} iters={o['num_iter'] - 1} x_passes={o['x_passes']} cache_hits={o['cache_hits']} "
       f"us/iter={1e3 * o['smo_ms'] / (o['num_iter'] - 1):.2f} grid={o['grid_blocks']}")
 seg = {"pivot rows requested->arrived (0->15)": t[:, 15] - t[:, 0], "K12 + scalar update (15->1)": t[:, 1] - t[:, 15],
-       "pass (1->2)": t[:, 2] - t[:, 1], "warp winners (2->3')": nxt[:, 3] - t[:, 2], "CTA barrier (3'->4')": nxt[:, 4] - nxt[:, 3],
+       "K12 + scalar update of a cached iteration (0->1)": t[:, 1] - t[:, 0], "pass (1->2)": t[:, 2] - t[:, 1], "warp winners (2->3')": nxt[:, 3] - t[:, 2], "CTA barrier (3'->4')": nxt[:, 4] - nxt[:, 3],
        "CTA fold: own slowest warp (4'->8')": nxt[:, 8] - nxt[:, 4], "partner's winners (8'->5')": nxt[:, 5] - nxt[:, 8],
        "record store (5'->6')": nxt[:, 6] - nxt[:, 5],
        "poll: warp 0's records seen (6'->11')": nxt[:, 11] - nxt[:, 6], "barrier: all warps' records (11'->12')": nxt[:, 12] - nxt[:, 11],
@@ -42,6 +42,8 @@ for label, mask in (("X-pass iterations", ~cached), ("cached iterations", cached
         continue
     print(f"{label} ({mask.sum()} in the sample)")
     for name, v in seg.items():
+        if ("(0->1)" in name) != (label == "cached iterations") and ("15" in name or "(0->1)" in name):
+            continue
         v = v[mask]; v = v[(v > 0) & (v < 10 ** 9)]
         if len(v):
             print(f"  {name:42s} median {np.median(v) / ghz / 1e3:7.3f} us   p90 {np.percentile(v, 90) / ghz / 1e3:7.3f} us")
