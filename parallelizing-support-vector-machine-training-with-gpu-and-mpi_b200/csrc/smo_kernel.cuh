@@ -167,6 +167,12 @@ __device__ __forceinline__ void group_dot2(const unsigned char *grp, int row_byt
 // A zero byte of the pivot adds u_k * 0 = +0 to its partial sum, i.e. nothing: the pass therefore walks only the tail
 // positions where one of the two pivots is non-zero (MNIST's border pixels: a handful out of 233), from four sub-lists
 // (one per c) that every warp builds at the top of the iteration.
+// a byte (any integer below 2^32) as a double without the conversion unit: it sits in the mantissa of 2^52, one DADD takes 2^52
+// away again (exact)
+__device__ __forceinline__ double u32_to_double(unsigned v)
+{
+    return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;
+}
 struct U8Lists {
     double2 *pp;            // [4][cap] weighted pivot bytes {w_k p_high_k, w_k p_low_k}
     unsigned short *kk;     // [4][cap] tail position k
@@ -211,7 +217,7 @@ __device__ __forceinline__ int u8_build_lists(const unsigned *__restrict__ xh_ta
                 if (nz[b]) {
                     const double wk = sh_wt[4 * w + b];
                     L.kk[e] = (unsigned short)(4 * w + b);
-                    L.pp[e] = make_double2(wk * (double)((th >> (8 * b)) & 255u), wk * (double)((tl >> (8 * b)) & 255u));
+                    L.pp[e] = make_double2(wk * u32_to_double((th >> (8 * b)) & 255u), wk * u32_to_double((tl >> (8 * b)) & 255u));
                     ++e;
                 }
             base += total;
@@ -237,8 +243,8 @@ __device__ __forceinline__ void u8_walk4(const unsigned char *rowtail, const dou
 {
     const uint2 k4 = *reinterpret_cast<const uint2 *>(kk + e);             // e is a multiple of 4: 8-byte aligned
     const double2 p0 = pp[e], p1 = pp[e + 1], p2 = pp[e + 2], p3 = pp[e + 3];
-    const double u0 = (double)rowtail[k4.x & 0xffffu], u1 = (double)rowtail[k4.x >> 16];
-    const double u2 = (double)rowtail[k4.y & 0xffffu], u3 = (double)rowtail[k4.y >> 16];
+    const double u0 = u32_to_double(rowtail[k4.x & 0xffffu]), u1 = u32_to_double(rowtail[k4.x >> 16]);
+    const double u2 = u32_to_double(rowtail[k4.y & 0xffffu]), u3 = u32_to_double(rowtail[k4.y >> 16]);
     ah = fma(u0, p0.x, ah); al = fma(u0, p0.y, al);
     ah = fma(u1, p1.x, ah); al = fma(u1, p1.y, al);
     ah = fma(u2, p2.x, ah); al = fma(u2, p2.y, al);

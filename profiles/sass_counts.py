@@ -10,9 +10,9 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "parallelizing-support-vector-machine-training-with-gpu-and-mpi_b200", "libsvmb200.so")
-HOT = ["smo_persistent_kernelIhLi8ELi2ELi256", "smo_persistent_kernelIfLi7ELi4ELi256", "smo_persistent_kernelIdLi13ELi1ELi256",
+HOT = ["smo_persistent_kernelIhLi5ELi1ELi256", "smo_persistent_kernelIfLi7ELi4ELi256", "smo_persistent_kernelIdLi13ELi1ELi256",
        "decision_tc_pipelined_kernel", "decision_kernelIdLi13", "decision_kernelIfLi7ELi4ELb1", "peer_rendezvous_kernel", "gather_raw_rows_kernel",
-       "u8_pack_kernel", "u8_norms_kernelILi8ELi2"]
+       "u8_pack_kernel", "u8_norms_kernel"]
 WATCH = ["UBLKCP", "UTCHMMA", "LDTM", "UTCBAR", "UTCATOMSWS", "REDUX", "IDP", "DFMA", "DADD", "PRMT", "LDS", "SHFL", "SYNCS", "STAS", "UCGABAR", "MAPA",
          "MEMBAR", "BAR", "LDG", "STG", "LD", "ST", "STL", "LDL", "MUFU", "F2F", "I2F"]
 
