@@ -839,7 +839,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const long long n = ctx->n;
     const int launches0 = ctx->launches;
 
-    // persistent grid: one CTA per SM, fewer for tiny problems
+    // persistent grid: one CTA per SM, fewer for tiny problems (the last 8 record places of the exchange stage the peer GPUs' records)
     const bool u8 = ctx->x_u8;
     const int Q = u8 ? 8 : q_for_pitch(ctx->pitch4, ctx->x_f64);
     const int QDEC = q_for_pitch(ctx->dec_pitch4, ctx->dec_f64);      // the decision kernels' row class (warm start)
@@ -871,7 +871,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     const size_t smem = smo_smem_bytes(ring_pitch4, kslots, warps, rps, tailw, tail_pitch, tail_rows);
     if (smem > (size_t)ctx->max_smem_optin) FAIL(SVMB200_ELIMIT, "row ring of %zu bytes does not fit in shared memory", smem);
     const long long n_own = n * (ctx->shard_rank + 1) / ctx->shard_world - n * ctx->shard_rank / ctx->shard_world;
-    int grid = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS), (n_own + 7) / 8));
+    int grid = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS - 8), (n_own + 7) / 8));
     // thread-block clusters of two CTAs (neighbouring SMs) halve the records of the exchange; the grid is then even
     int cluster = grid >= 2 ? 2 : 1;
 #ifdef SVM_TIMING
@@ -984,7 +984,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
     a.mailbox_copies = 1;
     for (int r = 0, first = 1; r < ctx->shard_world; ++r) {       // the clusters of the smallest grid among the GPUs (same rule as `grid` above)
         const long long own_r = n * (r + 1) / ctx->shard_world - n * r / ctx->shard_world;
-        int g = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS), (own_r + 7) / 8));
+        int g = (int)std::max<long long>(1, std::min<long long>(std::min(ctx->num_sms, SMO_MAX_RECS - 8), (own_r + 7) / 8));
         if (g >= 2) g /= 2;                                        // clusters of two (a launch that falls back to no clusters has more records)
         a.mailbox_copies = first ? std::min(SMO_MB_COPIES, g) : std::min(a.mailbox_copies, g);
         first = 0;

@@ -657,60 +657,40 @@ constexpr long long PEER_TIMEOUT_CLOCKS = 6000000000LL;   // ~3 s at 1.97 GHz: a
 
 // Poll `count` records starting at `recs` until every word carries `seq`, and stage their data words in shared memory.
 // Called by all warps of a leader CTA; warp w takes the groups of four records w, w + nwarps, ... (8 lanes x 16 bytes
-// cover a record, so a warp's load covers four records in one coalesced request).  Two sets of loads are kept in flight
-// half a round trip apart (set B is requested while set A travels, A is looked at, requested again, then B is looked
-// at, ...), so a record is seen at most half a round trip after it could have been; a group that is complete is staged
-// and not asked for again.
+// cover a record, so a warp's load covers four records in one coalesced request); a group that is complete is staged
+// and not asked for again.  (Two sets of loads in flight half a round trip apart were tried and were slower: loads that
+// poll one line from many SMs serialise in L2, see SMO_REC_COPIES.)
 // Returns false if the wait was given up: `abort_word` set by another CTA, or (deadline != 0) the clock ran out, in which
 // case this CTA sets the abort word so that every other wait on this GPU ends too.
-template <bool SYS, int G, bool STAGGER>
+template <bool SYS, int G>
 __device__ __forceinline__ bool poll_records_impl(const Rec *recs, int count, unsigned seq, unsigned (*stage)[REC_STRIDE], unsigned *abort_word,
                                                   long long deadline)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nwarps = (int)(blockDim.x >> 5);
     const int sub = lane >> 3, pair = lane & 7;
-    unsigned long long a0[G], a1[G], b0[STAGGER ? G : 1], b1[STAGGER ? G : 1];
+    unsigned long long w0[G], w1[G];
     unsigned pending = 0;                                  // warp-uniform: groups of this warp that are not complete yet
 #pragma unroll
     for (int u = 0; u < G; ++u)
         if ((warp + u * nwarps) * 4 < count) pending |= 1u << u;
-    auto request = [&](auto &x0, auto &x1) {
+    unsigned spins = 0;
+    while (pending) {
 #pragma unroll
         for (int u = 0; u < G; ++u) {
             const int r = (warp + u * nwarps) * 4 + sub;
-            if (((pending >> u) & 1u) && r < count) ld_pair<SYS>(&recs[r].w[2 * pair], x0[u], x1[u]);
+            if (((pending >> u) & 1u) && r < count) ld_pair<SYS>(&recs[r].w[2 * pair], w0[u], w1[u]);
         }
-    };
-    auto look = [&](const auto &x0, const auto &x1) {
 #pragma unroll
         for (int u = 0; u < G; ++u)
             if ((pending >> u) & 1u) {
                 const int r = (warp + u * nwarps) * 4 + sub;
-                const bool ok = r >= count || ((unsigned)(x0[u] >> 32) == seq && (unsigned)(x1[u] >> 32) == seq);
+                const bool ok = r >= count || ((unsigned)(w0[u] >> 32) == seq && (unsigned)(w1[u] >> 32) == seq);
                 if (__all_sync(FULL, ok)) {
-                    if (r < count) { stage[r][2 * pair] = (unsigned)x0[u]; stage[r][2 * pair + 1] = (unsigned)x1[u]; }
+                    if (r < count) { stage[r][2 * pair] = (unsigned)w0[u]; stage[r][2 * pair + 1] = (unsigned)w1[u]; }
                     pending &= ~(1u << u);
                 }
             }
-    };
-    unsigned spins = 0;
-    if (STAGGER && pending) {
-        request(a0, a1);
-        const long long t0 = clock64();
-        while (clock64() - t0 < 500) { }                  // about half an L2 round trip
-    }
-    while (pending) {
-        if (STAGGER) {
-            request(b0, b1);
-            look(a0, a1);
-            if (!pending) break;
-            request(a0, a1);
-            look(b0, b1);
-        } else {
-            request(a0, a1);
-            look(a0, a1);
-        }
         if ((++spins & 127u) == 0) {
             if (ld_relaxed_gpu_u32(abort_word)) return false;
             if (deadline && clock64() > deadline) { st_relaxed_gpu_u32(abort_word, 1u); return false; }
@@ -722,12 +702,12 @@ template <bool SYS>
 __device__ __forceinline__ bool poll_records(const Rec *recs, int count, unsigned seq, unsigned (*stage)[REC_STRIDE], unsigned *abort_word,
                                              long long deadline)
 {
-    // up to three groups per warp (clusters of two CTAs: 74 records = 19 groups over 8 warps; the peers' mailbox: 8 records): two
-    // sets of loads in flight; more (no clusters: 148 records): one set
+    // up to three groups per warp with clusters of two CTAs (74 records = 19 groups over 8 warps), one for the peers' mailbox
+    // (8 records), five without clusters (148 records)
     const int nwarps = (int)(blockDim.x >> 5);
-    if (SYS) return poll_records_impl<SYS, 1, false>(recs, count, seq, stage, abort_word, deadline);
-    if (count <= 12 * nwarps) return poll_records_impl<SYS, 3, false>(recs, count, seq, stage, abort_word, deadline);
-    return poll_records_impl<SYS, POLL_GROUPS_MAX, false>(recs, count, seq, stage, abort_word, deadline);
+    if (SYS) return poll_records_impl<SYS, 1>(recs, count, seq, stage, abort_word, deadline);
+    if (count <= 12 * nwarps) return poll_records_impl<SYS, 3>(recs, count, seq, stage, abort_word, deadline);
+    return poll_records_impl<SYS, POLL_GROUPS_MAX>(recs, count, seq, stage, abort_word, deadline);
 }
 // every warp folds the staged records by itself: lane l compares (f, idx) of records l, l + 32, ..., one REDUX round
 // per side finds the winning record, and every lane reads that record's payload
@@ -823,10 +803,12 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
             const int gen = (gather_no & 1) * SMO_MB_COPIES;
             if (cid < a.mailbox_copies && warp == 0) mailbox_store(a.peer_mailbox, a.peers, a.rank, (gen + cid) * 8, mine, seq2, lane);
             const int slot = (gen + cid % a.mailbox_copies) * 8;
-            __syncthreads();                               // the first level's staged words have been folded by every warp
-            const bool ok2 = poll_records<true>(a.mailbox + slot, a.peers, seq2, sh.recdata, a.abort_word, clock64() + PEER_TIMEOUT_CLOCKS);
+            // the peers' records are staged behind the first level's (at most 148 of the 160 places), which slower warps may
+            // still be folding: no CTA barrier in between
+            unsigned (*stage2)[REC_STRIDE] = sh.recdata + (SMO_MAX_RECS - 8);
+            const bool ok2 = poll_records<true>(a.mailbox + slot, a.peers, seq2, stage2, a.abort_word, clock64() + PEER_TIMEOUT_CLOCKS);
             ok = __syncthreads_and((ok && ok2) ? 1 : 0) != 0;
-            fold_staged(sh.recdata, a.peers, mine);
+            fold_staged(stage2, a.peers, mine);
         }
         if (cl > 1 && warp == 0 && lane == 0) {           // hop 4, sender
             Best lo = mine.lo, hi = mine.hi;

@@ -140,6 +140,30 @@ def _ranged_bytes(rng, n, d, ranges):
     return X
 
 
+def test_long_tails_in_short_tail_blocks(u8_solver, O):
+    """832 features without a shared range: the tails of 32 rows do not fit beside nothing else in shared memory, so a warp's
+    32-row block gets its tails in blocks of 16 rows whose sums are parked until the block ends; enough rows that every warp owns
+    several such blocks.  The first iterations bit for bit against the restated arithmetic (kernel rows of both pivots enter f)."""
+    d, n = 832, 24000
+    rng = np.random.default_rng(832)
+    ranges = np.asarray([1 + k % 254 for k in range(d)])
+    X = _ranged_bytes(rng, n, d, ranges)
+    w = rng.normal(size=d)
+    score = X.astype(np.float64) @ w
+    y = np.where(score > np.median(score), 1, -1).astype(np.int32)
+    gamma = 0.5 / d
+    u8_solver.set_train_u8(X, y)
+    R, M, T = O.u8_bind(X)
+    assert (M, T) == (0, d)
+    out = u8_solver.smo_train(gamma=gamma, C=1.0, max_iter=12, trace_cap=64, cache_rows=0)
+    xs, _, _ = O.scale(X)
+    dev = O.smo_train(xs, y, params=O.default_params(gamma=gamma, C=1.0, max_iter=12), arith=O.ARITH_DEVICE_U8, trace_cap=64, want_f=True)
+    assert out["num_iter"] == dev["num_iter"] and out["stop_reason"] == dev["stop_reason"] and dev["stop_reason"] in (4, "max_iter")
+    assert np.array_equal(u8_solver.get_trace(64), dev["trace"])
+    assert np.array_equal(out["alpha"], dev["alpha"]) and out["b"] == dev["b"]
+    assert np.array_equal(u8_solver.get_f(), dev["f"])
+
+
 @pytest.mark.parametrize("d,kind", [(1, "tail"), (4, "tail"), (30, "tail"), (100, "main"), (257, "mixed"), (600, "tail"),
                                     (770, "mixed"), (832, "main"), (832, "tail")])
 def test_other_feature_counts_and_layouts(u8_solver, O, d, kind):
