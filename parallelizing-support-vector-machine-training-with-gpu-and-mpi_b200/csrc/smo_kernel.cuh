@@ -463,15 +463,16 @@ __device__ __forceinline__ PairStep pair_update(int y_h, int y_l, double a_h, do
 
 // ---- the record exchange ---------------------------------------------------------------------
 // The one grid-wide synchronisation of an iteration, in four hops:
-//   1. CTA: warp winners (REDUX) -> shared memory -> warp 0 folds them;
-//   2. cluster (two CTAs on neighbouring SMs): the non-leader CTA writes its winners into the leader's shared memory
-//      (distributed shared memory, st.shared::cluster) and arrives on the leader's mbarrier; the leader folds the two;
-//   3. grid: the leader stores ONE 128-byte record per cluster (74 on a B200) and polls the others' records directly --
-//      no arrival counter, one L2 round trip after the last record lands.  A record is 16 words of 8 bytes, each
-//      {32 data bits, 32-bit exchange number}: an aligned 8-byte access is single-copy atomic, so a word that shows the
+//   1. warp: winners by REDUX (both sides side by side) -> shared memory of the cluster's LEADER CTA: the leader's warps write
+//      locally, the warps of the other CTA (two CTAs on neighbouring SMs form a cluster) through distributed shared memory
+//      (st.async: the bytes are counted on the leader's mbarrier, no fence);
+//   2. cluster: the leader's warp 0 folds the up to 32 entries in one REDUX round;
+//   3. grid: the leader stores ONE 128-byte record per cluster (74 on a B200), in SMO_REC_COPIES copies, and polls the others'
+//      records directly -- no arrival counter, one L2 round trip after the last record lands.  A record is 16 words of 8 bytes,
+//      each {32 data bits, 32-bit exchange number}: an aligned 8-byte access is single-copy atomic, so a word that shows the
 //      right number also shows its data and a reader that is too early simply re-reads.  The poll is warp-wide and
 //      coalesced (8 lanes x 16 bytes = one record, four records per load), which keeps the number of L2 requests per
-//      record line at one per leader and round;
+//      record line at one per polling leader and round;
 //   4. cluster: the leader writes the grid's winners into its partner's shared memory and arrives on its mbarrier.
 // With a cluster size of 1 (tiny grids, or a device that cannot co-schedule the clusters) hops 2 and 4 fall away.
 constexpr int REC_WORDS = 16;
@@ -627,8 +628,8 @@ constexpr int POLL_GROUPS_MAX = 5;        // groups of four records a warp polls
 constexpr int REC_STRIDE = REC_WORDS + 1;
 
 struct __align__(16) Shared {
-    Best wlo[SMO_MAX_WARPS], whi[SMO_MAX_WARPS];  // per-warp winners of this CTA's rows
-    Best plo, phi;                                // cluster leader: the partner CTA's winners (written through DSMEM)
+    Best wlo[2 * SMO_MAX_WARPS], whi[2 * SMO_MAX_WARPS];  // per-warp winners of this CTA's rows; cluster leader: behind them (from
+                                                  // [warps of a CTA] on) the partner CTA's, written through DSMEM
     Best rlo, rhi;                                // partner CTA: the grid's winners (written through DSMEM by the leader)
     uint64_t bar_in, bar_out;                     // mbarriers of the two cluster hops
     double k12;                                   // K12 of a cached iteration, read from L2 by one thread of the CTA
@@ -754,33 +755,34 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
     const bool leader = crank == 0;
     Rec *recs = a.rec + (size_t)(gather_no & 1) * SMO_REC_COPIES * SMO_MAX_RECS;      // [copy][record] of this generation
 
-    // hop 1: this CTA's winners
+    // hop 1: every warp's winners.  Hop 2 rides along: the warps of the non-leader CTA write theirs straight into the leader's
+    // shared memory (behind the leader's own warps' entries), counted on the leader's mbarrier, so one fold by the leader's warp 0
+    // covers the cluster
     best_warp_reduce(mine);
-    if (lane == 0) { sh.wlo[warp] = mine.lo; sh.whi[warp] = mine.hi; }
+    if (leader) {
+        if (lane == 0) { sh.wlo[warp] = mine.lo; sh.whi[warp] = mine.hi; }
+    } else if (lane == 0) {
+        const uint32_t bar = dsmem_addr(&sh.bar_in, 0);
+        dsmem_put_best(dsmem_addr(&sh.wlo[nwarps + warp], 0), mine.lo, bar);
+        dsmem_put_best(dsmem_addr(&sh.whi[nwarps + warp], 0), mine.hi, bar);
+        if (warp == 0) mbar_expect_tx(&sh.bar_out, BEST_PAIR_BYTES);       // arms this CTA's barrier for hop 4
+    }
     SVM_STAMP(3);
-    __syncthreads();
-    SVM_STAMP(4);
-    if (warp == 0) {
-        LocalBest b;
-        best_init(b);
-        if (lane < nwarps) { b.lo = sh.wlo[lane]; b.hi = sh.whi[lane]; }
-        best_warp_reduce(b);
-        SVM_STAMP(8);
-        if (!leader) {
-            // hop 2, sender: winners into the leader's shared memory, counted on the leader's mbarrier
-            if (lane == 0) {
-                const uint32_t bar = dsmem_addr(&sh.bar_in, 0);
-                dsmem_put_best(dsmem_addr(&sh.plo, 0), b.lo, bar);
-                dsmem_put_best(dsmem_addr(&sh.phi, 0), b.hi, bar);
-                mbar_expect_tx(&sh.bar_out, BEST_PAIR_BYTES);              // arms this CTA's barrier for hop 4
-            }
-        } else {
-            if (cl > 1) {                                  // hop 2, receiver
-                if (lane == 0) mbar_expect_tx(&sh.bar_in, BEST_PAIR_BYTES);
+    if (leader) {
+        __syncthreads();
+        SVM_STAMP(4);
+        if (warp == 0) {
+            bool got = true;
+            if (cl > 1) {                                  // the partner's entries
+                if (lane == 0) mbar_expect_tx(&sh.bar_in, (unsigned)nwarps * BEST_PAIR_BYTES);
                 __syncwarp();
-                if (!mbar_wait_abortable(&sh.bar_in, parity, a.abort_word)) b.lo.idx = b.hi.idx = IDX_NONE;
-                best_merge(b, sh.plo, sh.phi);
+                got = mbar_wait_abortable(&sh.bar_in, parity, a.abort_word);
             }
+            SVM_STAMP(8);
+            LocalBest b;
+            best_init(b);
+            if (lane < nwarps || (got && lane < (int)cl * nwarps)) { b.lo = sh.wlo[lane]; b.hi = sh.whi[lane]; }
+            best_warp_reduce(b);
             SVM_STAMP(5);
             rec_store_copies(recs, cid, b, seq, lane);                     // hop 3: publish
             SVM_STAMP(6);

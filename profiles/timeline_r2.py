@@ -1,7 +1,7 @@
 """Per-phase clock64 timeline of CTA 0 (a cluster leader) with the cluster exchange (profiling build
 libsvmb200_timing.so; never loaded by the product).   python profiles/timeline_r2.py N ITERS CACHE_ROWS [storage]
-Stamps of exchange g: 3 warp winners in shared memory, 4 after the CTA barrier, 8 CTA's winners folded, 5 partner's winners
-folded in (hop 2), 6 record stored, 11 warp 0's share of the records seen, 12 every warp's share staged (barrier), 13 all
+Stamps of exchange g: 3 warp winners in shared memory, 4 after the CTA barrier, 8 the partner CTA's warp winners have arrived,
+5 the cluster's winners folded, 6 record stored, 11 warp 0's share of the records seen, 12 every warp's share staged (barrier), 13 all
 records folded, 7 exchange done;
 of the iteration that follows: 0 loop top, 15 pivot rows arrived, 1 scalar update done, 2 pass done."""
 import ctypes as C, os, sys
@@ -30,7 +30,7 @@ print(f"n={n} storage={storage} iters={o['num_iter'] - 1} x_passes={o['x_passes'
       f"us/iter={1e3 * o['smo_ms'] / (o['num_iter'] - 1):.2f} grid={o['grid_blocks']}")
 seg = {"pivot rows requested->arrived (0->15)": t[:, 15] - t[:, 0], "K12 + scalar update (15->1)": t[:, 1] - t[:, 15],
        "K12 + scalar update of a cached iteration (0->1)": t[:, 1] - t[:, 0], "pass (1->2)": t[:, 2] - t[:, 1], "warp winners (2->3')": nxt[:, 3] - t[:, 2], "CTA barrier (3'->4')": nxt[:, 4] - nxt[:, 3],
-       "CTA fold: own slowest warp (4'->8')": nxt[:, 8] - nxt[:, 4], "partner's winners (8'->5')": nxt[:, 5] - nxt[:, 8],
+       "partner's warp winners there (4'->8')": nxt[:, 8] - nxt[:, 4], "fold of the cluster's warps (8'->5')": nxt[:, 5] - nxt[:, 8],
        "record store (5'->6')": nxt[:, 6] - nxt[:, 5],
        "poll: warp 0's records seen (6'->11')": nxt[:, 11] - nxt[:, 6], "barrier: all warps' records (11'->12')": nxt[:, 12] - nxt[:, 11],
        "fold of all records (12'->13')": nxt[:, 13] - nxt[:, 12], "to partner, done (13'->7')": nxt[:, 7] - nxt[:, 13],
