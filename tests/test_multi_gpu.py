@@ -36,6 +36,27 @@ def test_row_sharded_smo_is_bit_identical_to_one_gpu(world, tmp_path):
     assert len({r["correct"] for r in allres}) == 1
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [40, 200])
+def test_row_sharded_tiny_problems(n, tmp_path):
+    """Grids of a few CTAs per GPU: fewer clusters than the 16 mailbox copies (one cluster at n = 40: a single copy; 6 at
+    n = 200), same results as one GPU."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = tmp_path / "mgpu_tiny.json"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29420 + n % 7), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(n), str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    allres = json.load(open(out))
+    assert len(allres) == 2
+    for res in allres:
+        for label in ("cache_off", "cache_on", "cache_small"):
+            v = res[label]
+            assert v["iters"] == v["ref_iters"], (label, v)
+            assert v["alpha_equal"] and v["b_equal"] and v["trace_equal"] and v["sv_equal"], (label, v)
+
+
 @pytest.mark.parametrize("world,n", [(2, 11), (3, 100)])
 def test_row_sharding_host_logic_over_gloo(world, n, tmp_path):
     """CPU: the plumbing around the sharded solver (IPC-handle all_gather, row ranges, alpha all_gather, model install)."""
