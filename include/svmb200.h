@@ -42,7 +42,8 @@ extern "C" {
 #define SVMB200_STOP_INFEASIBLE  2  /* infeasible U and V                   main3.cpp:246 */
 #define SVMB200_STOP_ETA         3  /* non positive eta                     main3.cpp:253 */
 #define SVMB200_STOP_MAX_ITER    4  /* num_iter > max_iter                  main3.cpp:283 */
-#define SVMB200_STOP_PEER_LOST   5  /* row sharding only: a peer GPU's record never arrived (no counterpart) */
+#define SVMB200_STOP_PEER_LOST   5  /* a record of the exchange never arrived (~3 s): a peer GPU is gone (row sharding), or part of
+                                      this GPU's own grid never ran (the GPU is shared with other work).  No counterpart in the reference */
 
 typedef struct svmb200_ctx svmb200_ctx;
 

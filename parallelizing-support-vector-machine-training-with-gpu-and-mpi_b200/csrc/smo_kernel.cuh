@@ -790,7 +790,9 @@ __device__ __forceinline__ bool exchange(const SmoArgs &a, Shared &sh, LocalBest
     }
     bool ok = true;
     if (leader) {
-        ok = poll_records<false>(recs + (size_t)(cid % SMO_REC_COPIES) * SMO_MAX_RECS, NC, seq, sh.recdata, a.abort_word, 0);
+        // (the deadline: on a GPU shared with other work part of the grid may never run)
+        ok = poll_records<false>(recs + (size_t)(cid % SMO_REC_COPIES) * SMO_MAX_RECS, NC, seq, sh.recdata, a.abort_word,
+                                 clock64() + PEER_TIMEOUT_CLOCKS);
         SVM_STAMP(11);
         ok = __syncthreads_and(ok ? 1 : 0) != 0;          // every warp's share is staged
         SVM_STAMP(12);
