@@ -9,7 +9,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "aux_kernels.cuh"
@@ -51,6 +53,13 @@ struct svmb200_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     std::string err;
+    // device buffers of the training set are recycled inside the context instead of going back to the driver: a context that is
+    // given one training set after the other (the cascade's stages: ~30 buffers per stage) would otherwise spend its time in
+    // cudaFree / cudaMalloc, which serialise in the driver when several processes share a box.  All work of a context is on one
+    // stream, so a recycled buffer is handed out in stream order.
+    std::unordered_map<void *, size_t> pool_live;     // buffers handed out by dev_alloc: their sizes
+    std::multimap<size_t, void *> pool_idle;          // buffers given back by dev_free, by size
+    size_t pool_idle_bytes = 0;
 
     // training set
     long long n = 0;
@@ -174,10 +183,54 @@ static int ensure_work(svmb200_ctx *ctx, int which, size_t bytes)
     return 0;
 }
 
+static const size_t POOL_IDLE_MAX = (size_t)2 << 30;       // idle buffers kept: at most 2 GiB
+
+static void pool_trim(svmb200_ctx *ctx, size_t keep_bytes)
+{
+    while (ctx->pool_idle_bytes > keep_bytes && !ctx->pool_idle.empty()) {
+        auto it = std::prev(ctx->pool_idle.end());              // the largest first
+        cudaFree(it->second);
+        ctx->pool_idle_bytes -= it->first;
+        ctx->pool_idle.erase(it);
+    }
+}
+// a buffer of at least `bytes`: an idle one that is not more than twice as large, else a new one
+template <typename T>
+static int dev_alloc(svmb200_ctx *ctx, T **p, size_t bytes)
+{
+    bytes = (std::max<size_t>(bytes, 1) + 255) & ~(size_t)255;
+    auto it = ctx->pool_idle.lower_bound(bytes);
+    if (it != ctx->pool_idle.end() && it->first <= 2 * bytes + ((size_t)1 << 16)) {
+        *p = static_cast<T *>(it->second);
+        ctx->pool_live[it->second] = it->first;
+        ctx->pool_idle_bytes -= it->first;
+        ctx->pool_idle.erase(it);
+        return 0;
+    }
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, bytes);
+    if (e != cudaSuccess) {                                     // out of memory: give the idle buffers back and try once more
+        (void)cudaGetLastError();
+        pool_trim(ctx, 0);
+        e = cudaMalloc(&q, bytes);
+    }
+    CK(e);
+    ctx->pool_live[q] = bytes;
+    *p = static_cast<T *>(q);
+    return 0;
+}
 template <typename T>
 static int dev_free(svmb200_ctx *ctx, T *&p)
 {
-    if (p) CK(cudaFree(p));
+    if (!p) return 0;
+    auto it = ctx->pool_live.find((void *)p);
+    if (it == ctx->pool_live.end()) CK(cudaFree(p));           // not from dev_alloc (the row cache, work areas)
+    else {
+        ctx->pool_idle.emplace(it->second, (void *)p);
+        ctx->pool_idle_bytes += it->second;
+        ctx->pool_live.erase(it);
+        pool_trim(ctx, POOL_IDLE_MAX);
+    }
     p = nullptr;
     return 0;
 }
@@ -260,6 +313,7 @@ void svmb200_destroy(svmb200_ctx *ctx)
     cudaFree(ctx->svX); cudaFree(ctx->svcoef); cudaFree(ctx->scratch);
     cudaFree(ctx->work[0]); cudaFree(ctx->work[1]); cudaFree(ctx->svP);
     cudaFree(ctx->u8_nmain); cudaFree(ctx->u8_pos); cudaFree(ctx->u8_src); cudaFree(ctx->u8_ntail); cudaFree(ctx->u8_wt); cudaFree(ctx->Xdec);
+    pool_trim(ctx, 0);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1); cudaEventDestroy(ctx->ev2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -292,17 +346,17 @@ static int alloc_train(svmb200_ctx *ctx, long long n, int d)
         ctx->sv_alloc = 0;          // the support-vector block was sized for the old row pitch
         ctx->svX_bytes = 0;
         const int pitch4 = u8 ? 0 : dec_pitch4;                  // uint8 rows: known (and X allocated) once the statistics are
-        if (!u8) CK(cudaMalloc(&ctx->X, (size_t)n * pitch4 * 16));
-        CK(cudaMalloc(&ctx->y, (size_t)n * sizeof(int)));
-        CK(cudaMalloc(&ctx->sqn, (size_t)n * sizeof(double)));
-        CK(cudaMalloc(&ctx->f, (size_t)n * sizeof(double)));
-        CK(cudaMalloc(&ctx->alpha, (size_t)n * sizeof(double)));
-        CK(cudaMalloc(&ctx->cacheq, (size_t)n * sizeof(long long)));
-        CK(cudaMalloc(&ctx->minv, (size_t)d * sizeof(double)));
-        CK(cudaMalloc(&ctx->maxv, (size_t)d * sizeof(double)));
+        if (!u8) if (int rc = dev_alloc(ctx, &ctx->X, (size_t)n * pitch4 * 16)) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->y, (size_t)n * sizeof(int))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->sqn, (size_t)n * sizeof(double))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->f, (size_t)n * sizeof(double))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->alpha, (size_t)n * sizeof(double))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->cacheq, (size_t)n * sizeof(long long))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->minv, (size_t)d * sizeof(double))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->maxv, (size_t)d * sizeof(double))) return rc;
         if (u8) {
-            CK(cudaMalloc(&ctx->u8_nmain, (size_t)n * sizeof(int)));
-            CK(cudaMalloc(&ctx->u8_ntail, (size_t)n * sizeof(double)));
+            if (int rc = dev_alloc(ctx, &ctx->u8_nmain, (size_t)n * sizeof(int))) return rc;
+            if (int rc = dev_alloc(ctx, &ctx->u8_ntail, (size_t)n * sizeof(double))) return rc;
         }
         ctx->n = n;
         ctx->d = d;
@@ -397,10 +451,10 @@ static int pack_u8_rows(svmb200_ctx *ctx, const unsigned char *raw, long long n)
     ctx->u8_R = R; ctx->u8_M = M; ctx->u8_T = T; ctx->u8_mw = mw; ctx->u8_tw = tw; ctx->u8_tail_pitch = tail_pitch; ctx->u8_wR = sR * sR;
     ctx->pitch4 = row_bytes / 16;                   // bytes of a row over both arrays (accounting only)
     if (dev_free(ctx, ctx->u8_src) || dev_free(ctx, ctx->u8_pos) || dev_free(ctx, ctx->u8_wt) || dev_free(ctx, ctx->X)) return SVMB200_ECUDA;
-    CK(cudaMalloc(&ctx->u8_src, src.size() * sizeof(int)));
-    CK(cudaMalloc(&ctx->u8_pos, pos.size() * sizeof(int)));
-    CK(cudaMalloc(&ctx->u8_wt, wt.size() * sizeof(double)));
-    CK(cudaMalloc(&ctx->X, std::max<size_t>((size_t)n * row_bytes, 256)));
+    if (int rc = dev_alloc(ctx, &ctx->u8_src, src.size() * sizeof(int))) return rc;
+    if (int rc = dev_alloc(ctx, &ctx->u8_pos, pos.size() * sizeof(int))) return rc;
+    if (int rc = dev_alloc(ctx, &ctx->u8_wt, wt.size() * sizeof(double))) return rc;
+    if (int rc = dev_alloc(ctx, &ctx->X, std::max<size_t>((size_t)n * row_bytes, 256))) return rc;
     CK(cudaMemcpyAsync(ctx->u8_src, src.data(), src.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->u8_pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->u8_wt, wt.data(), wt.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
@@ -796,10 +850,10 @@ static int build_sv_block(svmb200_ctx *ctx, const std::vector<int> &ids, const d
         ctx->sv_alloc = 0;
         ctx->svX_bytes = 0;
         const int cap = std::max(nsv, 1024);
-        CK(cudaMalloc(&ctx->svX, (size_t)cap * ctx->dec_pitch4 * 16));
+        if (int rc = dev_alloc(ctx, &ctx->svX, (size_t)cap * ctx->dec_pitch4 * 16)) return rc;
         ctx->svX_bytes = (size_t)cap * ctx->dec_pitch4 * 16;
-        CK(cudaMalloc(&ctx->svcoef, (size_t)cap * sizeof(double)));
-        CK(cudaMalloc(&ctx->svn, (size_t)cap * sizeof(double)));
+        if (int rc = dev_alloc(ctx, &ctx->svcoef, (size_t)cap * sizeof(double))) return rc;
+        if (int rc = dev_alloc(ctx, &ctx->svn, (size_t)cap * sizeof(double))) return rc;
         ctx->sv_alloc = cap;
     }
     if (nsv == 0) return 0;
@@ -928,7 +982,7 @@ extern "C" int svmb200_smo_train(svmb200_ctx *ctx, const svmb200_params *params,
         CK(cudaGetLastError());
         const void *Xd = ctx->X;
         if (u8) {               // the decision kernel walks scaled FP64 rows: one copy of all rows, kept until the next upload
-            if (!ctx->Xdec) CK(cudaMalloc(&ctx->Xdec, (size_t)n * ctx->dec_pitch4 * 16));
+            if (!ctx->Xdec) if (int rc = dev_alloc(ctx, &ctx->Xdec, (size_t)n * ctx->dec_pitch4 * 16)) return rc;
             if (!ctx->xdec_valid) {
                 const long long total = n * ctx->dec_pitch4;
                 u8_gather_scale_kernel<<<(int)std::min<long long>((total + 255) / 256, (long long)ctx->num_sms * 16), 256, 0, ctx->stream>>>(
