@@ -201,3 +201,21 @@ def test_second_order_selection_restatement(O, dataset):
     assert np.max(np.abs(two["alpha"] - one["alpha"])) <= 1e-3 * 10.0
     # the first pair: i_high as in the first-order rule, i_low by gain
     assert two["trace"][0][0] == one["i_high"] or two["trace"][0][0] == O.smo_train(xs, y, params=O.default_params(max_iter=1))["i_high"]
+
+
+@pytest.mark.parametrize("n", [256, 2000])
+def test_second_order_selection_agrees_with_libsvm(O, dataset, n):
+    """The reference has no second-order rule, so its restatement is checked from outside as well: LIBSVM (through scikit-learn;
+    its working-set selection is the rule of Fan, Chen, Lin 2005 that wss = 2 restates) on the same scaled rows, with its stop
+    tolerance set to this solver's 2 tau, must end with the same support-vector set and bias."""
+    svm = pytest.importorskip("sklearn.svm")
+    X, _, y = dataset(n)
+    xs, _, _ = O.scale(X)
+    two = O.smo_train(xs, y, params=O.default_params(wss=2))
+    clf = svm.SVC(C=10.0, kernel="rbf", gamma=0.00125, tol=2e-5, shrinking=False, cache_size=500).fit(xs, y)
+    assert np.array_equal(np.sort(clf.support_), O.sv_indices(two["alpha"]))
+    assert abs(-clf.intercept_[0] - two["b"]) <= 2e-4 * max(1.0, abs(two["b"]))      # decision = sum alpha y K - b here, + intercept there
+    alpha_sk = np.zeros(len(y))
+    alpha_sk[clf.support_] = np.abs(clf.dual_coef_[0])
+    assert np.max(np.abs(alpha_sk - two["alpha"])) <= 5e-3 * 10.0                       # both stop at a gap of 2e-5: alphas agree to the tolerance
+    assert abs(int(clf.n_iter_[0]) - (two["num_iter"] - 1)) <= 0.25 * two["num_iter"]   # the same rule: a similar number of steps
